@@ -185,7 +185,7 @@ def irreps_dim(irreps: Sequence[Tuple[int, int, int]]) -> int:
 def tp_paths(irreps1: Sequence[Tuple[int, int, int]], lmax: int, target: Sequence[Tuple[int, int, int]]):
     """'uvu' paths of gnn/mace.py:286-314 for irreps2 = spherical harmonics up to lmax.
 
-    Returns list of (i1, l1, l2, l3) in the reference's weight order (stable sort by output irrep; generation order
+    Returns list of (i1, l1, l2, l3, p3) in the reference's weight order (stable sort by output irrep; generation order
     i1 asc, l2 asc, l3 asc inside), i.e. path p owns weight columns [p*mul, (p+1)*mul).
     """
     tset = {(l, p) for _, l, p in target}
@@ -197,7 +197,7 @@ def tp_paths(irreps1: Sequence[Tuple[int, int, int]], lmax: int, target: Sequenc
                 if (l3, p1 * p2) in tset:
                     gen.append((i1, l1, l2, l3, p1 * p2))
     order = sorted(range(len(gen)), key=lambda k: (gen[k][3], gen[k][4]))  # Irrep order (l, p); stable
-    return [gen[k][:4] for k in order]
+    return [gen[k] for k in order]
 
 
 # ------------------------------------------------------------------------------------------------------------------
