@@ -1,0 +1,178 @@
+// Generic fp32 block GEMM over blocked (m-major) irreps layouts.
+// Replaces e3nn o3.Linear (einsum 'zui,uw->zwi' per irrep -> cuBLAS bmm; gnn/blocks.py:516-521,552-559,471-476,276-279)
+// and the torch.nn.Linear layers of the radial MLP (gnn/blocks.py:538-549).
+// CUDA-core path: 128x32x16 tiles, 256 threads, 4x4 register micro-tile, float4 smem reads.
+#include "eeg_common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 32, BK = 16, APAD = 4;
+
+struct BlockDesc {
+  int rows;      // 2l+1
+  int k;         // mul_in
+  int nout;      // mul_out
+  int in_off, out_off;
+  int64_t w_off;
+  float scale;
+  int tile_begin;  // first tile index of this block
+  int n_col_tiles;
+};
+
+struct LinearParams {
+  BlockDesc b[EEG_MAX_L];
+  int n_blocks;
+  int in_stride, out_stride;
+  int transB, act;
+};
+
+__global__ void __launch_bounds__(256) k_block_linear(const float* __restrict__ in, const float* __restrict__ W,
+                                                      const float* __restrict__ bias, const float* __restrict__ residual,
+                                                      float* __restrict__ out, int64_t N, LinearParams P) {
+  __shared__ __align__(16) float As[BK][BM + APAD];
+  __shared__ __align__(16) float Bs[BK][BN];
+  int tile = blockIdx.x;
+  int bi = 0;
+#pragma unroll
+  for (int q = 1; q < EEG_MAX_L; ++q)
+    if (q < P.n_blocks && tile >= P.b[q].tile_begin) bi = q;
+  const BlockDesc d = P.b[bi];
+  tile -= d.tile_begin;
+  const int col_tile = tile % d.n_col_tiles;
+  const int64_t row0 = (int64_t)(tile / d.n_col_tiles) * BM;
+  const int n0 = col_tile * BN;
+  const int64_t total_rows = N * d.rows;
+  const int t = threadIdx.x;
+  const int tx = t & 7, ty = t >> 3;
+
+  // A-load mapping: 4 lanes per row (4 float4 = 16 k), 64 rows per iteration, 2 iterations
+  const int a_kq = t & 3, a_r = t >> 2;
+  const float* a_ptr[2];
+  bool a_ok[2];
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    int64_t r = row0 + a_r + 64 * it;
+    a_ok[it] = r < total_rows;
+    int64_t n = a_ok[it] ? r / d.rows : 0;
+    int m = a_ok[it] ? (int)(r - n * d.rows) : 0;
+    a_ptr[it] = in + n * P.in_stride + d.in_off + (int64_t)m * d.k + a_kq * 4;
+  }
+  const float* Wb = W + d.w_off;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < d.k; k0 += BK) {
+    // ---- A tile (transposed into smem)
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (a_ok[it] && k0 + a_kq * 4 < d.k) v = __ldg(reinterpret_cast<const float4*>(a_ptr[it] + k0));
+      int r = a_r + 64 * it;
+      As[a_kq * 4 + 0][r] = v.x;
+      As[a_kq * 4 + 1][r] = v.y;
+      As[a_kq * 4 + 2][r] = v.z;
+      As[a_kq * 4 + 3][r] = v.w;
+    }
+    // ---- B tile
+    if (!P.transB) {
+      // W[k][n]: 16 rows x 32 cols = 128 float4; threads 0..127
+      if (t < 128) {
+        int kk = t >> 3, c4 = (t & 7) * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k0 + kk < d.k && n0 + c4 < d.nout) v = __ldg(reinterpret_cast<const float4*>(Wb + (int64_t)(k0 + kk) * d.nout + n0 + c4));
+        *reinterpret_cast<float4*>(&Bs[kk][c4]) = v;
+      }
+    } else {
+      // W[n][k]: 32 cols x 16 k = 128 float4 along k
+      if (t < 128) {
+        int c = t >> 2, kq = t & 3;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (n0 + c < d.nout && k0 + kq * 4 < d.k) v = __ldg(reinterpret_cast<const float4*>(Wb + (int64_t)(n0 + c) * d.k + k0 + kq * 4));
+        Bs[kq * 4 + 0][c] = v.x;
+        Bs[kq * 4 + 1][c] = v.y;
+        Bs[kq * 4 + 2][c] = v.z;
+        Bs[kq * 4 + 3][c] = v.w;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  const int col = n0 + tx * 4;
+  if (col >= d.nout) return;
+  float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (bias != nullptr && bi == 0) bv = __ldg(reinterpret_cast<const float4*>(bias + col));
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int64_t r = row0 + ty * 4 + i;
+    if (r >= total_rows) continue;
+    int64_t n = r / d.rows;
+    int m = (int)(r - n * d.rows);
+    int64_t o = n * P.out_stride + d.out_off + (int64_t)m * d.nout + col;
+    float4 v = make_float4(fmaf(acc[i][0], d.scale, bv.x), fmaf(acc[i][1], d.scale, bv.y), fmaf(acc[i][2], d.scale, bv.z),
+                           fmaf(acc[i][3], d.scale, bv.w));
+    if (P.act == 1) {
+      v.x = eeg_silu(v.x); v.y = eeg_silu(v.y); v.z = eeg_silu(v.z); v.w = eeg_silu(v.w);
+    }
+    if (residual != nullptr) {
+      float4 rr = __ldg(reinterpret_cast<const float4*>(residual + o));
+      v.x += rr.x; v.y += rr.y; v.z += rr.z; v.w += rr.w;
+    }
+    *reinterpret_cast<float4*>(out + o) = v;
+  }
+}
+
+}  // namespace
+
+extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off,
+                                    const float* host_scale, const float* bias, int transB, int act, const float* residual,
+                                    float* out, const EegLayout* lout, int64_t N, void* stream) {
+  EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_fwd: layout mismatch");
+  if (N == 0) return 0;
+  LinearParams P;
+  P.n_blocks = lin->n_blocks;
+  P.in_stride = lin->stride;
+  P.out_stride = lout->stride;
+  P.transB = transB;
+  P.act = act;
+  EEG_REQUIRE(lin->stride % 4 == 0 && lout->stride % 4 == 0, "eeg_block_linear_fwd: strides must be multiples of 4");
+  int64_t tiles = 0;
+  for (int b = 0; b < P.n_blocks; ++b) {
+    EEG_REQUIRE(lin->rows[b] == lout->rows[b], "eeg_block_linear_fwd: block %d rows differ", b);
+    EEG_REQUIRE(lin->mul[b] % 4 == 0 && lout->mul[b] % 4 == 0 && lin->off[b] % 4 == 0 && lout->off[b] % 4 == 0 &&
+                    host_w_off[b] % 4 == 0,
+                "eeg_block_linear_fwd: block %d not float4-aligned", b);
+    BlockDesc& d = P.b[b];
+    d.rows = lin->rows[b];
+    d.k = lin->mul[b];
+    d.nout = lout->mul[b];
+    d.in_off = lin->off[b];
+    d.out_off = lout->off[b];
+    d.w_off = host_w_off[b];
+    d.scale = host_scale[b];
+    d.tile_begin = (int)tiles;
+    d.n_col_tiles = (d.nout + BN - 1) / BN;
+    int64_t row_tiles = (N * d.rows + BM - 1) / BM;
+    tiles += (d.nout > 0 && d.k > 0) ? row_tiles * d.n_col_tiles : 0;
+    if (d.nout == 0 || d.k == 0) d.n_col_tiles = 1;
+    EEG_REQUIRE(tiles < (1LL << 31), "eeg_block_linear_fwd: too many tiles");
+  }
+  if (tiles == 0) return 0;
+  k_block_linear<<<(unsigned)tiles, 256, 0, (cudaStream_t)stream>>>(in, W, bias, residual, out, N, P);
+  EEG_CHECK_LAUNCH("eeg_block_linear_fwd");
+  return 0;
+}

@@ -1,0 +1,93 @@
+/* eeg_b200.h - C ABI of the B200-native EnergyEquivGNN hot path (libeeg_b200.so).
+ *
+ * The reference (igrega348/energy-equiv-lattice-gnn) has no native code and no FFI: its arithmetic lives in
+ * e3nn / torch_scatter / opt_einsum calls made from gnn/model.py, gnn/blocks.py and gnn/mace.py.  Each entry point
+ * below replaces one such call site (cited per function).  Conventions:
+ *   - every pointer is a DEVICE pointer unless named host_*; tensors are dense row-major fp32, indices as stated;
+ *   - no allocation inside: caller passes outputs and workspace; `stream` is a cudaStream_t passed as void*;
+ *   - return 0 on success, non-zero error code otherwise; text via eeg_last_error() (thread-local);
+ *   - node-feature layout ("blocked, m-major"): per node a row  concat_l [ (2l+1) x mul_l ]  with element
+ *     (l, m, u) at  off_l + m*mul_l + u.  With mul_l == C for all l this is [N, (lmax+1)^2, C].
+ */
+#ifndef EEG_B200_H
+#define EEG_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EEG_MAX_L 8 /* max number of irrep blocks in one layout */
+
+const char* eeg_last_error(void);
+int eeg_abi_version(void);
+
+/* Blocked layout descriptor (host struct, passed by pointer). */
+typedef struct EegLayout {
+  int32_t n_blocks;            /* number of irrep blocks */
+  int32_t rows[EEG_MAX_L];     /* 2l+1 per block */
+  int32_t mul[EEG_MAX_L];      /* multiplicity per block */
+  int32_t off[EEG_MAX_L];      /* float offset of the block inside a node row */
+  int32_t stride;              /* floats per node row */
+} EegLayout;
+
+/* ---- graph indexing: replaces torch_scatter's unsorted atomics (gnn/blocks.py:595-597) with a CSR ------------------
+ * edge_index int64 [2,E] (row 0 sender, row 1 receiver; gnn/mace.py:345).  perm = edge ids stably sorted by receiver
+ * (== torch.sort(receiver, stable=True).indices, bit-exact), row_ptr = exclusive cumsum of bincount(receiver).
+ * ws: at least eeg_csr_workspace_bytes(E, N) bytes. */
+size_t eeg_csr_workspace_bytes(int64_t E, int64_t N);
+int eeg_csr_build(const int64_t* edge_index, int64_t E, int64_t N, int32_t* row_ptr /*[N+1]*/, int32_t* perm /*[E]*/,
+                  void* ws, size_t ws_bytes, void* stream);
+/* batch int64 [N] non-decreasing graph id (PyG Batch.batch; gnn/model.py:100-106) -> graph_ptr int32 [G+1] */
+int eeg_graph_ptr(const int64_t* batch, int64_t N, int64_t G, int32_t* graph_ptr, void* stream);
+
+/* ---- edge featurisation: gnn/mace.py:338-352 + gnn/model.py:146-157 (e3nn soft_one_hot_linspace x2, SphericalHarmonics)
+ * Outputs are written in CSR order (slot j <-> edge perm[j]):  Y [E, ystride] (ystride = (lmax+1)^2 rounded up to 4),
+ * f [E, 2*nbasis] (length basis first), sender_sorted int32 [E]. */
+int eeg_edge_featurize(const float* pos /*[N,3]*/, const int64_t* edge_index, const float* shifts /*[E,3]*/,
+                       const float* radius /*[E]*/, const int32_t* perm, int64_t E, int lmax, int nbasis, float len_end,
+                       float rmax, float* Y, int ystride, float* f, int32_t* sender_sorted, void* stream);
+
+/* ---- generic fp32 block GEMM over blocked layouts: e3nn o3.Linear (gnn/blocks.py:516-521,552-559,471-476,276-279,
+ * gnn/model.py:82-86) and torch.nn.Linear of the radial MLP (gnn/blocks.py:538-549).
+ * For block b: out[n, b, m, w] = act( scale[b] * sum_u in[n, b, m, u] * W_b[u, w] + bias_b[w] ) (+ residual[n,b,m,w])
+ * W_b at W + w_off[b]; row-major [mul_in, mul_out] (transB=0) or [mul_out, mul_in] (transB=1, torch.nn.Linear).
+ * bias may be NULL; bias applies to block 0 only (0e scalars). act: 0 none, 1 SiLU.  residual may be NULL (layout = out). */
+int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off,
+                         const float* host_scale, const float* bias, int transB, int act, const float* residual,
+                         float* out, const EegLayout* lout, int64_t N, void* stream);
+
+/* ---- channelwise tensor product + scatter-sum: e3nn TensorProduct 'uvu' + torch_scatter (gnn/blocks.py:591-597)
+ * h [N, (lmax_in+1)^2, C] sender features (after linear_up), Y/w/sender in CSR order, w [E, n_paths, C].
+ * M [N, rows_total, C] with rows laid out per l3 as [(2l3+1), n_paths(l3)] (EegLayout with mul = n_paths*C).
+ * (lmax_in, lmax) must be a generated combination: (0,4),(4,4),(0,3),(3,3).  C multiple of 32. */
+int eeg_tp_scatter_fwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w,
+                       const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, float* M, int64_t N,
+                       void* stream);
+
+/* ---- symmetric contraction (product basis): gnn/mace.py:112-277
+ * eeg_sc_coefficients: T[n_coef, C] = A_csr @ Wflat[n_wrows, C]   (A = symmetrised U tensors, built by the host)
+ * eeg_sym_contract_fwd: x [N, D, C] -> out [N, D, C]; (lmax, nu) must be generated: (4,3), (3,3). */
+int eeg_sc_coefficients(const int32_t* a_row_ptr, const int32_t* a_col, const float* a_val, int n_coef,
+                        const float* Wflat, int C, float* T, void* stream);
+int eeg_sym_contract_fwd(int lmax, int nu, int C, const float* x, const float* T, float* out, int64_t N, void* stream);
+
+/* ---- gated non-linearity: e3nn.nn.Gate (gnn/blocks.py:268-282).  z layout: block0 mul = S + G (scalars then gates),
+ * blocks l>=1 mul = g_l with sum g_l = G; out layout: block0 mul = S, blocks l>=1 mul g_l.  act = c * silu. */
+int eeg_gate_fwd(const float* z, const EegLayout* lz, float* out, const EegLayout* lout, int n_scalars, float act_const,
+                 int64_t N, void* stream);
+
+/* ---- pooling + tail: scatter(mean) (gnn/model.py:100-106), final o3.Linear (:108), Spherical_to_Cartesian +
+ * Cart_4_to_Mandel (gnn/blocks.py:392-442) folded into P [n_q, 36], PositiveLayer (gnn/blocks.py:185-229).
+ * o: node features (layout lo); Wq [sum_b mul_b*q_b] per-block [mul_b, q_b] (q_b = 0 for unused blocks), bias [q_0];
+ * q layout = concat_b [q_b, rows_b] (mul-major, e3nn);  positive: 0 none, 1 A^2, 2 A^4, 3 (I+A/2)^2, 4 (I+A/4)^4.
+ * reduce: 0 mean, 1 sum. */
+int eeg_pool_tail_fwd(const float* o, const EegLayout* lo, const int32_t* graph_ptr, const float* Wq,
+                      const int32_t* host_qmul, const float* host_qscale, const float* bias, const float* P /*[nq,36]*/,
+                      int positive, int reduce, float* q_out /*[G,nq] or NULL*/, float* A_out /*[G,36] or NULL*/,
+                      float* C_out /*[G,36]*/, int64_t G, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
