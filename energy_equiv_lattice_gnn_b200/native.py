@@ -1,0 +1,181 @@
+"""ctypes binding of libeeg_b200.so (the C ABI declared in include/eeg_b200.h).
+
+There is no CPU fallback: if the library is missing, or a tensor is not a contiguous CUDA tensor of the stated dtype,
+the call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libeeg_b200.so")
+EEG_MAX_L = 8
+
+SYMBOLS = [
+    "eeg_last_error", "eeg_abi_version", "eeg_csr_workspace_bytes", "eeg_csr_build", "eeg_graph_ptr",
+    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
+    "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd",
+]
+
+
+class EegLayout(C.Structure):
+    _fields_ = [("n_blocks", C.c_int32), ("rows", C.c_int32 * EEG_MAX_L), ("mul", C.c_int32 * EEG_MAX_L),
+                ("off", C.c_int32 * EEG_MAX_L), ("stride", C.c_int32)]
+
+
+def make_layout(rows: Sequence[int], mul: Sequence[int]) -> EegLayout:
+    """Blocked m-major layout: block b = [rows_b, mul_b] at the running offset."""
+    assert len(rows) == len(mul) <= EEG_MAX_L
+    lay = EegLayout()
+    lay.n_blocks = len(rows)
+    off = 0
+    for b, (r, m) in enumerate(zip(rows, mul)):
+        lay.rows[b], lay.mul[b], lay.off[b] = r, m, off
+        off += r * m
+    lay.stride = off
+    return lay
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m energy_equiv_lattice_gnn_b200.build` "
+                "(or __graft_entry__.build()); there is no CPU/PyTorch fallback for the hot path.")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.eeg_last_error.restype = C.c_char_p
+        _lib.eeg_csr_workspace_bytes.restype = C.c_size_t
+        _lib.eeg_csr_workspace_bytes.argtypes = [C.c_int64, C.c_int64]
+        for s in SYMBOLS:
+            getattr(_lib, s)  # fail loudly on a stale library
+    return _lib
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (code {rc}): {lib().eeg_last_error().decode()}")
+
+
+def _p(t: Optional[torch.Tensor], dtype=None):
+    if t is None:
+        return C.c_void_p(0)
+    if not t.is_cuda:
+        raise RuntimeError("libeeg_b200 needs CUDA tensors (no CPU fallback)")
+    if not t.is_contiguous():
+        raise RuntimeError("libeeg_b200 needs contiguous tensors")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"expected dtype {dtype}, got {t.dtype}")
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+f32, i32, i64 = torch.float32, torch.int32, torch.int64
+
+
+def csr_build(edge_index: torch.Tensor, n_nodes: int):
+    E = edge_index.shape[1]
+    dev = edge_index.device
+    row_ptr = torch.empty(n_nodes + 1, dtype=i32, device=dev)
+    perm = torch.empty(E, dtype=i32, device=dev)
+    nbytes = lib().eeg_csr_workspace_bytes(E, n_nodes)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    _check(lib().eeg_csr_build(_p(edge_index, i64), C.c_int64(E), C.c_int64(n_nodes), _p(row_ptr), _p(perm), _p(ws),
+                               C.c_size_t(nbytes), _stream()), "eeg_csr_build")
+    return row_ptr, perm
+
+
+def graph_ptr(batch: torch.Tensor, num_graphs: int):
+    gp = torch.empty(num_graphs + 1, dtype=i32, device=batch.device)
+    _check(lib().eeg_graph_ptr(_p(batch, i64), C.c_int64(batch.shape[0]), C.c_int64(num_graphs), _p(gp), _stream()), "eeg_graph_ptr")
+    return gp
+
+
+def node_embed(node_attrs, W, b):
+    N, Cch = node_attrs.shape[0], W.shape[0]
+    out = torch.empty(N, Cch, dtype=f32, device=node_attrs.device)
+    _check(lib().eeg_node_embed_fwd(_p(node_attrs, f32), _p(W, f32), _p(b, f32), _p(out), C.c_int64(N), C.c_int(Cch), _stream()),
+           "eeg_node_embed_fwd")
+    return out
+
+
+def edge_featurize(pos, edge_index, shifts, radius, perm, lmax, nbasis, len_end, rmax):
+    E = edge_index.shape[1]
+    D = (lmax + 1) ** 2
+    ystride = (D + 3) // 4 * 4
+    dev = pos.device
+    Y = torch.empty(E, ystride, dtype=f32, device=dev)
+    f = torch.empty(E, 2 * nbasis, dtype=f32, device=dev)
+    snd = torch.empty(E, dtype=i32, device=dev)
+    _check(lib().eeg_edge_featurize(_p(pos, f32), _p(edge_index, i64), _p(shifts, f32), _p(radius, f32), _p(perm, i32),
+                                    C.c_int64(E), C.c_int(lmax), C.c_int(nbasis), C.c_float(len_end), C.c_float(rmax),
+                                    _p(Y), C.c_int(ystride), _p(f), _p(snd), _stream()), "eeg_edge_featurize")
+    return Y, f, snd
+
+
+def block_linear(x, lin: EegLayout, W, w_off: Sequence[int], scale: Sequence[float], lout: EegLayout, n_rows: int,
+                 bias=None, transB=False, act=0, residual=None, out=None):
+    nb = lin.n_blocks
+    if out is None:
+        out = torch.empty(n_rows, lout.stride, dtype=f32, device=x.device)
+    woff = (C.c_int64 * EEG_MAX_L)(*list(w_off) + [0] * (EEG_MAX_L - nb))
+    sc = (C.c_float * EEG_MAX_L)(*list(scale) + [0.0] * (EEG_MAX_L - nb))
+    _check(lib().eeg_block_linear_fwd(_p(x, f32), C.byref(lin), _p(W, f32), woff, sc, _p(bias, f32), C.c_int(int(transB)),
+                                      C.c_int(act), _p(residual, f32), _p(out, f32), C.byref(lout), C.c_int64(n_rows),
+                                      _stream()), "eeg_block_linear_fwd")
+    return out
+
+
+def tp_scatter(lmax_in, lmax, Cch, h, Y, w, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes):
+    M = torch.empty(n_nodes, rows_total * Cch, dtype=f32, device=h.device)
+    _check(lib().eeg_tp_scatter_fwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]),
+                                    _p(w, f32), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm), _p(M),
+                                    C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_fwd")
+    return M
+
+
+def sc_coefficients(a_row_ptr, a_col, a_val, n_coef, Wflat, Cch):
+    T = torch.empty(Cch, n_coef, dtype=f32, device=Wflat.device)
+    _check(lib().eeg_sc_coefficients(_p(a_row_ptr, i32), _p(a_col, i32), _p(a_val, f32), C.c_int(n_coef), _p(Wflat, f32),
+                                     C.c_int(Cch), _p(T), _stream()), "eeg_sc_coefficients")
+    return T
+
+
+def sym_contract(lmax, nu, Cch, x, T, n_nodes):
+    out = torch.empty_like(x)
+    _check(lib().eeg_sym_contract_fwd(C.c_int(lmax), C.c_int(nu), C.c_int(Cch), _p(x, f32), _p(T, f32), _p(out),
+                                      C.c_int64(n_nodes), _stream()), "eeg_sym_contract_fwd")
+    return out
+
+
+def gate(z, lz: EegLayout, lout: EegLayout, n_scalars: int, act_const: float, n_nodes: int):
+    out = torch.empty(n_nodes, lout.stride, dtype=f32, device=z.device)
+    _check(lib().eeg_gate_fwd(_p(z, f32), C.byref(lz), _p(out), C.byref(lout), C.c_int(n_scalars), C.c_float(act_const),
+                              C.c_int64(n_nodes), _stream()), "eeg_gate_fwd")
+    return out
+
+
+def pool_tail(o, lo: EegLayout, gp, Wq, qmul: Sequence[int], qscale: Sequence[float], bias, P, positive: int, reduce: int,
+              num_graphs: int, want_aux: bool = False):
+    dev = o.device
+    nq = sum(q * lo.rows[b] for b, q in enumerate(qmul))
+    Cout = torch.empty(num_graphs, 6, 6, dtype=f32, device=dev)
+    q_out = torch.empty(num_graphs, nq, dtype=f32, device=dev) if want_aux else None
+    A_out = torch.empty(num_graphs, 6, 6, dtype=f32, device=dev) if want_aux else None
+    nb = lo.n_blocks
+    qm = (C.c_int32 * EEG_MAX_L)(*list(qmul) + [0] * (EEG_MAX_L - nb))
+    qs = (C.c_float * EEG_MAX_L)(*list(qscale) + [0.0] * (EEG_MAX_L - nb))
+    _check(lib().eeg_pool_tail_fwd(_p(o, f32), C.byref(lo), _p(gp, i32), _p(Wq, f32), qm, qs, _p(bias, f32), _p(P, f32),
+                                   C.c_int(positive), C.c_int(reduce), _p(q_out), _p(A_out), _p(Cout), C.c_int64(num_graphs),
+                                   _stream()), "eeg_pool_tail_fwd")
+    return Cout, q_out, A_out

@@ -41,6 +41,10 @@ int eeg_csr_build(const int64_t* edge_index, int64_t E, int64_t N, int32_t* row_
 /* batch int64 [N] non-decreasing graph id (PyG Batch.batch; gnn/model.py:100-106) -> graph_ptr int32 [G+1] */
 int eeg_graph_ptr(const int64_t* batch, int64_t N, int64_t G, int32_t* graph_ptr, void* stream);
 
+/* ---- node embedding: torch.nn.Linear(1, C) on node_attrs [N,1] (gnn/model.py:122,142): out[n,c] = a[n]*W[c] + b[c] */
+int eeg_node_embed_fwd(const float* node_attrs, const float* W /*[C,1]*/, const float* b /*[C]*/, float* out /*[N,C]*/,
+                       int64_t N, int C, void* stream);
+
 /* ---- edge featurisation: gnn/mace.py:338-352 + gnn/model.py:146-157 (e3nn soft_one_hot_linspace x2, SphericalHarmonics)
  * Outputs are written in CSR order (slot j <-> edge perm[j]):  Y [E, ystride] (ystride = (lmax+1)^2 rounded up to 4),
  * f [E, 2*nbasis] (length basis first), sender_sorted int32 [E]. */
@@ -66,7 +70,7 @@ int eeg_tp_scatter_fwd(int lmax_in, int lmax, int C, const float* h, const float
                        void* stream);
 
 /* ---- symmetric contraction (product basis): gnn/mace.py:112-277
- * eeg_sc_coefficients: T[n_coef, C] = A_csr @ Wflat[n_wrows, C]   (A = symmetrised U tensors, built by the host)
+ * eeg_sc_coefficients: T[C, n_coef] (channel-major) = (A_csr @ Wflat[n_wrows, C])^T   (A = symmetrised U tensors, built by the host)
  * eeg_sym_contract_fwd: x [N, D, C] -> out [N, D, C]; (lmax, nu) must be generated: (4,3), (3,3). */
 int eeg_sc_coefficients(const int32_t* a_row_ptr, const int32_t* a_col, const float* a_val, int n_coef,
                         const float* Wflat, int C, float* T, void* stream);
