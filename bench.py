@@ -1,0 +1,273 @@
+#!/usr/bin/env python
+"""bench.py - EnergyEquivGNN forward + stiffness throughput (lattices/s) on B200, BASELINE.json config 2:
+1024 synthetic periodic lattices (30 nodes / 60 struts -> 120 directed edges each) per GPU, default hyper-parameters
+(scripts/train_main.py:25-52), fp32, random-init weights (torch.manual_seed(0)).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--lattices 1024]
+
+One JSON line on stdout (rank 0).  `--impl reference` times the CPU restatement of the reference (oracle/) on the
+host cores on a bounded sample of the same workload (the reference's own stack - e3nn/torch_scatter - is not
+installable on this box).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "lattices/sec fwd+stiffness"
+UNIT = "lattices/s"
+N_NODES = 30
+CPU_SAMPLE = 16  # lattices per CPU-baseline step (BASELINE.json config 1)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_reference_run(steps: int, warmup: int, seed0: int):
+    """Oracle forward on CPU_SAMPLE lattices, all host threads. Returns (lattices/s, ms/step, threads)."""
+    from energy_equiv_lattice_gnn_b200.data import synthetic_batch
+    from tests.util import make_pair
+    batch, rmax = synthetic_batch(range(seed0, seed0 + CPU_SAMPLE), N_NODES)
+    oracle, _ = make_pair(rmax, dtype=torch.float32)
+    oracle.eval()
+    with torch.no_grad():
+        for _ in range(warmup):
+            oracle(batch)
+        ts = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            oracle(batch)
+            ts.append(time.perf_counter() - t0)
+    ms = 1e3 * sum(ts) / len(ts)
+    return CPU_SAMPLE / (ms / 1e3), ms, torch.get_num_threads()
+
+
+class ClockSampler:
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(gpu_index)],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name).read().strip().splitlines() if r.strip()]
+        os.unlink(self.f.name)
+        sm, reasons = [], set()
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1]))
+                out["sm_max_mhz"] = float(r[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.strip().lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            sm.sort()
+            out["sm_mhz"] = sm[len(sm) // 2]
+        out["reasons"] = sorted(reasons)
+        out["samples"] = len(sm)
+        return out
+
+
+def algorithmic_model(model, n_nodes: int, n_edges: int):
+    """Per-kernel algorithmic bytes / flops for one launch, keyed by timing tag."""
+    C, D = model.C, (model.lmax + 1) ** 2
+    P1 = len(model._tp[-1]["paths"])
+    rows1 = model._tp[-1]["rows_total"]
+    cg1 = sum(len(v) for v in model._tp[-1]["cg"].values())
+    ncoef = model._wmap["n_coef"]
+    N, E = n_nodes, n_edges
+    f4 = 4
+    out = {
+        "L1.tp_scatter": dict(bytes=f4 * (N * D * C + E * (P1 * C + D + 1) + N * rows1 * C + N), flops=E * C * (2 * cg1 + 2 * rows1)),
+        "L1.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef),
+        "L0.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef),
+        "L1.mlp2": dict(bytes=f4 * (E * 64 + E * P1 * C + 64 * P1 * C), flops=2 * E * 64 * P1 * C),
+        "L1.interaction_linear": dict(bytes=f4 * (N * rows1 * C + N * D * C + rows1 * C * C // D), flops=2 * N * rows1 * C * C),
+    }
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--lattices", type=int, default=1024, help="lattices per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    config = {"workload": f"EnergyEquivGNN inference fwd+stiffness, batch {args.lattices} synthetic lattices/GPU "
+                          f"({N_NODES} nodes, {2 * N_NODES} struts, {4 * N_NODES} directed edges each), default hyper-parameters "
+                          "(lmax=4, 32 channels, correlation 3, 2 message passes), fp32 [BASELINE.json configs[1]]",
+              "lattices_per_gpu": args.lattices, "nodes_per_lattice": N_NODES, "edges_per_lattice": 4 * N_NODES,
+              "l2": "per-step working set (~2.7 GB of intermediates at 1024 lattices) >> 126 MB L2; inputs rotate over 2 distinct batches"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        torch.set_num_threads(os.cpu_count() or 1)
+        val, ms, thr = cpu_reference_run(max(1, args.steps), max(1, args.warmup), 2000)
+        line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": val, "unit": UNIT, "cores": thr, "kind": "port",
+                                 "sample": f"{CPU_SAMPLE} lattices/step of the same synthetic workload (seeds 2000..), oracle/ CPU restatement of the "
+                                           "reference formulation (dense w3j tensor product, U.W.x contraction), torch fp32"},
+                "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the hot path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    from energy_equiv_lattice_gnn_b200 import EnergyEquivGNN, native
+    from energy_equiv_lattice_gnn_b200.data import synthetic_batch
+    from energy_equiv_lattice_gnn_b200.params import default_params
+    native.lib()
+
+    G = args.lattices
+    host_batches = []
+    rmax = 0.0
+    for k in range(2):
+        seed0 = 2000 + (2 * rank + k) * G
+        b, r = synthetic_batch(range(seed0, seed0 + G), N_NODES)
+        host_batches.append(b.pin_memory())
+        rmax = max(rmax, r)
+    params = default_params(max_edge_radius=rmax)
+    torch.manual_seed(0)
+    model = EnergyEquivGNN(params).to(dev).eval()
+    dev_batches = [b.to(dev) for b in host_batches]
+    n_nodes, n_edges = dev_batches[0].positions.shape[0], dev_batches[0].edge_index.shape[1]
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        with torch.no_grad():
+            for i in range(warmup):
+                fn(i)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(steps):
+                fn(i)
+            e1.record()
+            barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if dist is not None:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    results = []
+
+    def step_resident(i):
+        results.append(model(dev_batches[i % 2])["stiffness"])
+        if len(results) > 4:
+            results.pop(0)
+
+    def step_e2e(i):
+        hb = host_batches[i % 2]
+        out = model(hb.to(dev, non_blocking=True))["stiffness"]
+        return out.cpu()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = native.launch_count
+    ms_total = timed(step_resident, args.steps, max(3, args.warmup))
+    launches = native.launch_count - l0
+    launches_timed = launches * args.steps // (args.steps + max(3, args.warmup))
+    clocks = sampler.stop() if sampler else {}
+    ms_e2e = timed(step_e2e, args.steps, max(3, args.warmup))
+    hb = host_batches[0]
+    h2d = sum(getattr(hb, k).numel() * getattr(hb, k).element_size() for k in ("positions", "node_attrs", "edge_index", "shifts", "edge_attr", "batch"))
+    d2h = G * 36 * 4
+
+    # per-kernel durations, CUDA events on the launching stream, same steps
+    native.start_profile()
+    with torch.no_grad():
+        for i in range(args.steps):
+            model(dev_batches[i % 2])
+    prof = native.stop_profile()
+    kern = {k: sum(v) / len(v) for k, v in prof.items()}
+    step_sum = sum(kern.values())
+    alg = algorithmic_model(model, n_nodes, n_edges)
+    peak, peak_src = measured_peaks()
+    top = max((k for k in kern if k in alg), key=lambda k: kern[k])
+    top_ms = kern[top]
+    achieved = alg[top]["bytes"] / (top_ms * 1e-3) / 1e9
+    roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peak_src, "ms_per_launch": top_ms, "share_of_step": top_ms / step_sum,
+                "algorithmic_bytes_per_launch": alg[top]["bytes"], "algorithmic_flops_per_launch": alg[top]["flops"],
+                "fp32_tflops_achieved": alg[top]["flops"] / (top_ms * 1e-3) / 1e12,
+                "note": "kernel is fp32-FMA bound, not HBM bound (SURVEY.md App. C); bytes-based fraction reported as the contract asks"}
+    kernels = {k: {"ms": round(v, 4), **({"GBps": round(alg[k]["bytes"] / v / 1e6, 1), "TFLOPs": round(alg[k]["flops"] / v / 1e9, 2)} if k in alg else {})}
+               for k, v in sorted(kern.items(), key=lambda kv: -kv[1])}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    ms_step = ms_total / args.steps
+    value = world * G / (ms_step * 1e-3)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": config, "clocks": clocks,
+            "e2e": {"value": world * G / (ms_e2e / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches_timed, "roofline": roofline, "kernels": kernels}
+    if world == 1 and not args.no_cpu_baseline:
+        torch.set_num_threads(os.cpu_count() or 1)
+        val, ms, thr = cpu_reference_run(3, 1, 2000)
+        line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": thr, "kind": "port", "ms_per_step": ms,
+                                "sample": f"{CPU_SAMPLE} lattices/step (seeds 2000..{2000 + CPU_SAMPLE - 1}) of the same workload, 1 warm-up + 3 timed, "
+                                          "oracle/ CPU restatement of the reference formulation, torch fp32"}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -151,9 +151,11 @@ def synthetic_lattice(seed: int, n_nodes: int = 30, n_struts: Optional[int] = No
     rank[order] = np.arange(len(order))
     chosen: List[int] = []
     chosen_set = set()
-    for n in range(N):  # each node's shortest candidate
-        m = np.where((I == n) | (J == n))[0]
-        best = m[np.argmin(rank[m])]
+    best_rank = np.full(N, len(order), dtype=np.int64)  # each node's shortest candidate
+    np.minimum.at(best_rank, I, rank)
+    np.minimum.at(best_rank, J, rank)
+    for n in range(N):
+        best = order[best_rank[n]]
         if best not in chosen_set:
             chosen_set.add(int(best))
             chosen.append(int(best))

@@ -151,6 +151,7 @@ class EnergyEquivGNN(torch.nn.Module):
         if hit is not None and hit[0] == key:
             return hit[1]
         Wflat = torch.cat([w.detach() for w in ws], 0).contiguous()
+        nv.set_tag(f'L{i}.sc_coefficients')
         T = nv.sc_coefficients(self._a_row_ptr, self._a_col, self._a_val, self._wmap["n_coef"], Wflat, self.C)
         self._cache[("sc", i)] = (key, T)
         return T
@@ -196,13 +197,17 @@ class EnergyEquivGNN(torch.nn.Module):
         edge_index = batch.edge_index.contiguous()
         N, G = batch.node_attrs.shape[0], int(batch.num_graphs)
         f32 = torch.float32
+        nv.set_tag('csr')
         row_ptr, perm = nv.csr_build(edge_index, N)
+        nv.set_tag('graph_ptr')
         gp = nv.graph_ptr(batch.batch.contiguous(), G)
+        nv.set_tag('edge_featurize')
         Y, f, snd = nv.edge_featurize(batch.positions.to(f32).contiguous(), edge_index, batch.shifts.to(f32).contiguous(),
                                       batch.edge_attr.to(f32).reshape(-1).contiguous(), perm, lmax, self.number_of_edge_basis,
                                       0.6, self.max_edge_radius)
         E = edge_index.shape[1]
         emb = self.node_ft_embedding
+        nv.set_tag('node_embed')
         h = nv.node_embed(batch.node_attrs.to(f32).contiguous(), emb.weight.detach().reshape(-1).contiguous(), emb.bias.detach())
         sC = 1.0 / math.sqrt(C)
         if save is not None:
@@ -211,6 +216,7 @@ class EnergyEquivGNN(torch.nn.Module):
             inter, prod = layer.interaction, layer.product
             lay_in = self._lay_h0 if i == 0 else self._lay_h
             nblk = lay_in.n_blocks
+            nv.set_tag(f'L{i}.linear_up')
             hup = nv.block_linear(h, lay_in, inter.linear_up.weight.detach(), [b * C * C for b in range(nblk)], [sC] * nblk, lay_in, N)
             # radial MLP (gnn/blocks.py:538-549,590)
             a, acts = f, [f]
@@ -220,17 +226,22 @@ class EnergyEquivGNN(torch.nn.Module):
                 lay_a = self._lay_f if j == 0 else self._lay_mlp
                 last = j == len(lins) - 1
                 lay_b = self._lay_w[i] if last else self._lay_mlp
+                nv.set_tag(f'L{i}.mlp{j}')
                 a = nv.block_linear(a, lay_a, lin.weight.detach(), [0], [1.0], lay_b, E,
                                     bias=None if lin.bias is None else lin.bias.detach(), transB=True, act=0 if last else 1)
                 acts.append(a)
             w = a
             plan = self._tp[i]
+            nv.set_tag(f'L{i}.tp_scatter')
             M = nv.tp_scatter(0 if i == 0 else lmax, lmax, C, hup, Y, w, snd, row_ptr, 1.0 / self.agg_norm_const, plan["rows_total"], N)
             n_l = [ps["n_paths"] for ps in plan["passes"]]
             woff = np.concatenate(([0], np.cumsum([n * C * C for n in n_l])))[:-1].tolist()
+            nv.set_tag(f'L{i}.interaction_linear')
             msg = nv.block_linear(M, self._lay_M[i], inter.linear.weight.detach(), woff, [1.0 / math.sqrt(n * C) for n in n_l],
                                   self._lay_h, N, bias=inter.linear.bias.detach())
+            nv.set_tag(f'L{i}.sym_contract')
             B = nv.sym_contract(lmax, self.correlation, C, msg, self._sc_table(i), N)
+            nv.set_tag(f'L{i}.product_linear')
             h_new = nv.block_linear(B, self._lay_h, prod.linear.weight.detach(), [b * C * C for b in range(lmax + 1)],
                                     [sC] * (lmax + 1), self._lay_h, N, residual=h if i > 0 else None)
             if save is not None:
@@ -240,11 +251,15 @@ class EnergyEquivGNN(torch.nn.Module):
         ro = head.nonlin_readout
         n_gates = C * lmax
         w1off = [0] + [C * (C + n_gates) + b * C * C for b in range(lmax)]
+        nv.set_tag('readout.linear_1')
         z = nv.block_linear(h, self._lay_h, ro.linear_1.weight.detach(), w1off, [sC] * (lmax + 1), self._lay_z, N)
+        nv.set_tag('readout.gate')
         g = nv.gate(z, self._lay_z, self._lay_g, C, NORM2MOM_SILU, N)
         w2off = np.concatenate(([0], np.cumsum([C * m for m in self.rmul])))[:-1].tolist()
+        nv.set_tag('readout.linear_2')
         o = nv.block_linear(g, self._lay_g, ro.linear_2.weight.detach(), w2off, [sC] * (lmax + 1), self._lay_o, N)
         qscale = [1.0 / math.sqrt(m) for m in self.rmul]
+        nv.set_tag('pool_tail')
         Cst, q, A = nv.pool_tail(o, self._lay_o, gp, head.linear.weight.detach(), self._qmul, qscale, head.linear.bias.detach(),
                                  self._tail_matrix(), _POSITIVE[self.params.positive_function],
                                  0 if self.params.global_reduction == "mean" else 1, G, want_aux=save is not None)

@@ -59,9 +59,54 @@ def lib() -> C.CDLL:
     return _lib
 
 
+# Optional per-entry-point CUDA-event timing (bench.py roofline leg) and launch accounting.
+# KERNELS_PER_CALL = kernels one C-ABI call launches (memsets excluded).
+KERNELS_PER_CALL = {"eeg_csr_build": 6, "eeg_graph_ptr": 1, "eeg_node_embed_fwd": 1, "eeg_edge_featurize": 1,
+                    "eeg_block_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
+                    "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1}
+launch_count = 0
+_events = None  # list of (name, tag, start_event, end_event) while profiling
+_tag = ""
+
+
+def set_tag(tag: str):
+    """Label subsequent calls (e.g. 'L1.mlp3') for the per-kernel timing table."""
+    global _tag
+    _tag = tag
+
+
+def start_profile():
+    global _events
+    _events = []
+
+
+def stop_profile():
+    """-> {tag or name: [ms, ...]} (synchronises)."""
+    global _events
+    torch.cuda.synchronize()
+    out = {}
+    for name, tag, a, b in _events:
+        out.setdefault(tag or name, []).append(a.elapsed_time(b))
+    _events = None
+    return out
+
+
 def _check(rc: int, what: str):
+    global launch_count
     if rc != 0:
         raise RuntimeError(f"{what} failed (code {rc}): {lib().eeg_last_error().decode()}")
+    launch_count += KERNELS_PER_CALL.get(what, 1)
+    if _events is not None and _events and _events[-1][3] is None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        _events[-1] = _events[-1][:3] + (ev,)
+
+
+def _begin(what: str):
+    if _events is not None:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        _events.append((what, _tag, ev, None))
 
 
 def _p(t: Optional[torch.Tensor], dtype=None):
@@ -90,6 +135,7 @@ def csr_build(edge_index: torch.Tensor, n_nodes: int):
     perm = torch.empty(E, dtype=i32, device=dev)
     nbytes = lib().eeg_csr_workspace_bytes(E, n_nodes)
     ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    _begin("eeg_csr_build")
     _check(lib().eeg_csr_build(_p(edge_index, i64), C.c_int64(E), C.c_int64(n_nodes), _p(row_ptr), _p(perm), _p(ws),
                                C.c_size_t(nbytes), _stream()), "eeg_csr_build")
     return row_ptr, perm
@@ -97,6 +143,7 @@ def csr_build(edge_index: torch.Tensor, n_nodes: int):
 
 def graph_ptr(batch: torch.Tensor, num_graphs: int):
     gp = torch.empty(num_graphs + 1, dtype=i32, device=batch.device)
+    _begin("eeg_graph_ptr")
     _check(lib().eeg_graph_ptr(_p(batch, i64), C.c_int64(batch.shape[0]), C.c_int64(num_graphs), _p(gp), _stream()), "eeg_graph_ptr")
     return gp
 
@@ -104,6 +151,7 @@ def graph_ptr(batch: torch.Tensor, num_graphs: int):
 def node_embed(node_attrs, W, b):
     N, Cch = node_attrs.shape[0], W.shape[0]
     out = torch.empty(N, Cch, dtype=f32, device=node_attrs.device)
+    _begin("eeg_node_embed_fwd")
     _check(lib().eeg_node_embed_fwd(_p(node_attrs, f32), _p(W, f32), _p(b, f32), _p(out), C.c_int64(N), C.c_int(Cch), _stream()),
            "eeg_node_embed_fwd")
     return out
@@ -117,6 +165,7 @@ def edge_featurize(pos, edge_index, shifts, radius, perm, lmax, nbasis, len_end,
     Y = torch.empty(E, ystride, dtype=f32, device=dev)
     f = torch.empty(E, 2 * nbasis, dtype=f32, device=dev)
     snd = torch.empty(E, dtype=i32, device=dev)
+    _begin("eeg_edge_featurize")
     _check(lib().eeg_edge_featurize(_p(pos, f32), _p(edge_index, i64), _p(shifts, f32), _p(radius, f32), _p(perm, i32),
                                     C.c_int64(E), C.c_int(lmax), C.c_int(nbasis), C.c_float(len_end), C.c_float(rmax),
                                     _p(Y), C.c_int(ystride), _p(f), _p(snd), _stream()), "eeg_edge_featurize")
@@ -130,6 +179,7 @@ def block_linear(x, lin: EegLayout, W, w_off: Sequence[int], scale: Sequence[flo
         out = torch.empty(n_rows, lout.stride, dtype=f32, device=x.device)
     woff = (C.c_int64 * EEG_MAX_L)(*list(w_off) + [0] * (EEG_MAX_L - nb))
     sc = (C.c_float * EEG_MAX_L)(*list(scale) + [0.0] * (EEG_MAX_L - nb))
+    _begin("eeg_block_linear_fwd")
     _check(lib().eeg_block_linear_fwd(_p(x, f32), C.byref(lin), _p(W, f32), woff, sc, _p(bias, f32), C.c_int(int(transB)),
                                       C.c_int(act), _p(residual, f32), _p(out, f32), C.byref(lout), C.c_int64(n_rows),
                                       _stream()), "eeg_block_linear_fwd")
@@ -138,6 +188,7 @@ def block_linear(x, lin: EegLayout, W, w_off: Sequence[int], scale: Sequence[flo
 
 def tp_scatter(lmax_in, lmax, Cch, h, Y, w, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes):
     M = torch.empty(n_nodes, rows_total * Cch, dtype=f32, device=h.device)
+    _begin("eeg_tp_scatter_fwd")
     _check(lib().eeg_tp_scatter_fwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]),
                                     _p(w, f32), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm), _p(M),
                                     C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_fwd")
@@ -146,6 +197,7 @@ def tp_scatter(lmax_in, lmax, Cch, h, Y, w, sender_sorted, row_ptr, inv_norm, ro
 
 def sc_coefficients(a_row_ptr, a_col, a_val, n_coef, Wflat, Cch):
     T = torch.empty(Cch, n_coef, dtype=f32, device=Wflat.device)
+    _begin("eeg_sc_coefficients")
     _check(lib().eeg_sc_coefficients(_p(a_row_ptr, i32), _p(a_col, i32), _p(a_val, f32), C.c_int(n_coef), _p(Wflat, f32),
                                      C.c_int(Cch), _p(T), _stream()), "eeg_sc_coefficients")
     return T
@@ -153,6 +205,7 @@ def sc_coefficients(a_row_ptr, a_col, a_val, n_coef, Wflat, Cch):
 
 def sym_contract(lmax, nu, Cch, x, T, n_nodes):
     out = torch.empty_like(x)
+    _begin("eeg_sym_contract_fwd")
     _check(lib().eeg_sym_contract_fwd(C.c_int(lmax), C.c_int(nu), C.c_int(Cch), _p(x, f32), _p(T, f32), _p(out),
                                       C.c_int64(n_nodes), _stream()), "eeg_sym_contract_fwd")
     return out
@@ -160,6 +213,7 @@ def sym_contract(lmax, nu, Cch, x, T, n_nodes):
 
 def gate(z, lz: EegLayout, lout: EegLayout, n_scalars: int, act_const: float, n_nodes: int):
     out = torch.empty(n_nodes, lout.stride, dtype=f32, device=z.device)
+    _begin("eeg_gate_fwd")
     _check(lib().eeg_gate_fwd(_p(z, f32), C.byref(lz), _p(out), C.byref(lout), C.c_int(n_scalars), C.c_float(act_const),
                               C.c_int64(n_nodes), _stream()), "eeg_gate_fwd")
     return out
@@ -175,6 +229,7 @@ def pool_tail(o, lo: EegLayout, gp, Wq, qmul: Sequence[int], qscale: Sequence[fl
     nb = lo.n_blocks
     qm = (C.c_int32 * EEG_MAX_L)(*list(qmul) + [0] * (EEG_MAX_L - nb))
     qs = (C.c_float * EEG_MAX_L)(*list(qscale) + [0.0] * (EEG_MAX_L - nb))
+    _begin("eeg_pool_tail_fwd")
     _check(lib().eeg_pool_tail_fwd(_p(o, f32), C.byref(lo), _p(gp, i32), _p(Wq, f32), qm, qs, _p(bias, f32), _p(P, f32),
                                    C.c_int(positive), C.c_int(reduce), _p(q_out), _p(A_out), _p(Cout), C.c_int64(num_graphs),
                                    _stream()), "eeg_pool_tail_fwd")
