@@ -126,7 +126,7 @@ class TensorProductUVU(torch.nn.Module):
             y = sh[:, l2 * l2:(l2 + 1) * (l2 + 1)]
             w = weight[:, woff:woff + mul]
             woff += mul
-            c = torch.as_tensor(cv.wigner_3j(l1, l2, l3), dtype=x1.dtype, device=x1.device)
+            c = torch.tensor(np.array(cv.wigner_3j(l1, l2, l3)), dtype=x1.dtype, device=x1.device)
             o = torch.einsum("zu,ijk,zui,zj->zuk", w, c, a, y) * math.sqrt(2 * l3 + 1)
             outs.append(o.reshape(x1.shape[0], -1))
         return torch.cat(outs, dim=-1)

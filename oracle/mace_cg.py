@@ -12,6 +12,7 @@ from __future__ import annotations
 
 from typing import List, Optional, Tuple
 
+import numpy as np
 import torch
 
 from energy_equiv_lattice_gnn_b200 import conventions as cv
@@ -45,7 +46,7 @@ def _wigner_nj(irrepss: List[List[Ir]], dtype, keep_last: Optional[List[Ir]] = N
             for ir_out in _ir_mul(ir_left, ir):
                 if keep_last is not None and ir_out not in keep_last:
                     continue
-                C = torch.as_tensor(cv.wigner_3j(ir_out[0], ir_left[0], ir[0]), dtype=dtype).clone()
+                C = torch.tensor(np.array(cv.wigner_3j(ir_out[0], ir_left[0], ir[0])), dtype=dtype)
                 C *= (2 * ir_out[0] + 1) ** 0.5
                 C = torch.einsum("jk,ijl->ikl", C_left.flatten(1), C)
                 C = C.reshape(2 * ir_out[0] + 1, *dims_left, 2 * ir[0] + 1)
