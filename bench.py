@@ -114,7 +114,7 @@ def algorithmic_model(model, n_nodes: int, n_edges: int):
         "L1.tp_scatter": dict(bytes=f4 * (N * D * C + E * (P1 * C + D + 1) + N * rows1 * C + N), flops=E * C * (2 * cg1 + 2 * rows1)),
         "L1.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef),
         "L0.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef),
-        "L1.mlp2": dict(bytes=f4 * (E * 64 + E * P1 * C + 64 * P1 * C), flops=2 * E * 64 * P1 * C),
+        "L1.radial_mlp": dict(bytes=f4 * (E * 12 + E * P1 * C + 2 * 64 * (64 + P1 * C)), flops=2 * E * (12 * 64 + 64 * 64 + 64 * P1 * C)),
         "L1.interaction_linear": dict(bytes=f4 * (N * rows1 * C + N * D * C + rows1 * C * C // D), flops=2 * N * rows1 * C * C),
     }
     return out

@@ -53,6 +53,8 @@ class EnergyEquivGNN(torch.nn.Module):
             raise ValueError(f"Unknown positive function: {params.positive_function}")
         if params.global_reduction not in ("mean", "sum"):
             raise ValueError(f"Unknown global reduction: {params.global_reduction}")
+        if int(params.inter_MLP_dim) != 64 or int(params.inter_MLP_layers) < 2 or 2 * int(params.num_edge_bases) > 16:
+            raise NotImplementedError("radial MLP kernel: inter_MLP_dim must be 64, inter_MLP_layers >= 2, 2*num_edge_bases <= 16")
         self.correlation = int(params.correlation)
         self.number_of_edge_basis = nb = int(params.num_edge_bases)
         self.max_edge_radius = float(params.max_edge_radius)
@@ -156,6 +158,20 @@ class EnergyEquivGNN(torch.nn.Module):
         self._cache[("sc", i)] = (key, T)
         return T
 
+    def _radial_image(self, i: int, lins):
+        """Packed hi/lo tcgen05 operand image of layer i's radial-MLP weights (cached on the weights' versions)."""
+        key = tuple((l.weight.data_ptr(), l.weight._version) for l in lins[1:]) + tuple((l.bias.data_ptr(), l.bias._version) for l in lins[1:-1])
+        hit = self._cache.get(("radial", i))
+        if hit is not None and hit[0] == key:
+            return hit[1], hit[2]
+        hidden = lins[1:-1]
+        Wh = torch.stack([l.weight.detach() for l in hidden]).contiguous() if hidden else None
+        bh = torch.stack([l.bias.detach() for l in hidden]).contiguous() if hidden else lins[0].bias.detach().new_zeros(1, lins[0].weight.shape[0])
+        nv.set_tag(f'L{i}.radial_pack')
+        img = nv.radial_pack(Wh, lins[-1].weight.detach().contiguous())
+        self._cache[("radial", i)] = (key, img, bh)
+        return img, bh
+
     def _tail_matrix(self) -> torch.Tensor:
         """P[nq, 36]: q -> Mandel matrix A (Spherical_to_Cartesian then Cart_4_to_Mandel, gnn/blocks.py:392-442)."""
         head = self.stiffness_head
@@ -218,19 +234,12 @@ class EnergyEquivGNN(torch.nn.Module):
             nblk = lay_in.n_blocks
             nv.set_tag(f'L{i}.linear_up')
             hup = nv.block_linear(h, lay_in, inter.linear_up.weight.detach(), [b * C * C for b in range(nblk)], [sC] * nblk, lay_in, N)
-            # radial MLP (gnn/blocks.py:538-549,590)
-            a, acts = f, [f]
-            mods = list(inter.conv_tp_weights)
-            lins = [m for m in mods if isinstance(m, torch.nn.Linear)]
-            for j, lin in enumerate(lins):
-                lay_a = self._lay_f if j == 0 else self._lay_mlp
-                last = j == len(lins) - 1
-                lay_b = self._lay_w[i] if last else self._lay_mlp
-                nv.set_tag(f'L{i}.mlp{j}')
-                a = nv.block_linear(a, lay_a, lin.weight.detach(), [0], [1.0], lay_b, E,
-                                    bias=None if lin.bias is None else lin.bias.detach(), transB=True, act=0 if last else 1)
-                acts.append(a)
-            w = a
+            # radial MLP (gnn/blocks.py:538-549,590): fused, last layers on tcgen05; output path-major w_t[P*C/32, E, 32]
+            lins = [m for m in inter.conv_tp_weights if isinstance(m, torch.nn.Linear)]
+            nv.set_tag(f'L{i}.radial_mlp')
+            img, bh = self._radial_image(i, lins)
+            w = nv.radial_mlp(f, lins[0].weight.detach(), lins[0].bias.detach(), bh, len(lins) - 2, img, lins[-1].weight.shape[0])
+            acts = None
             plan = self._tp[i]
             nv.set_tag(f'L{i}.tp_scatter')
             M = nv.tp_scatter(0 if i == 0 else lmax, lmax, C, hup, Y, w, snd, row_ptr, 1.0 / self.agg_norm_const, plan["rows_total"], N)

@@ -18,7 +18,7 @@ EEG_MAX_L = 8
 SYMBOLS = [
     "eeg_last_error", "eeg_abi_version", "eeg_csr_workspace_bytes", "eeg_csr_build", "eeg_graph_ptr",
     "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
-    "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd",
+    "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd", "eeg_radial_image_floats", "eeg_radial_pack", "eeg_radial_mlp_fwd",
 ]
 
 
@@ -63,7 +63,8 @@ def lib() -> C.CDLL:
 # KERNELS_PER_CALL = kernels one C-ABI call launches (memsets excluded).
 KERNELS_PER_CALL = {"eeg_csr_build": 6, "eeg_graph_ptr": 1, "eeg_node_embed_fwd": 1, "eeg_edge_featurize": 1,
                     "eeg_block_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
-                    "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1}
+                    "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1,
+                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1}
 launch_count = 0
 _events = None  # list of (name, tag, start_event, end_event) while profiling
 _tag = ""
@@ -186,12 +187,37 @@ def block_linear(x, lin: EegLayout, W, w_off: Sequence[int], scale: Sequence[flo
     return out
 
 
-def tp_scatter(lmax_in, lmax, Cch, h, Y, w, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes):
+def radial_pack(Wh: Optional[torch.Tensor], W2: torch.Tensor) -> torch.Tensor:
+    """Hidden 64x64 weights [n_hidden,64,64] (or None) + last-layer weight [n_out,64] -> staged hi/lo operand image."""
+    n_hidden = 0 if Wh is None else Wh.shape[0]
+    n_out, H = W2.shape
+    L = lib()
+    L.eeg_radial_image_floats.restype = C.c_int64
+    img = torch.empty(L.eeg_radial_image_floats(C.c_int(n_hidden), C.c_int(n_out)), dtype=f32, device=W2.device)
+    _begin("eeg_radial_pack")
+    _check(L.eeg_radial_pack(_p(Wh, f32), C.c_int(n_hidden), C.c_int(H), _p(W2, f32), C.c_int(n_out), _p(img), _stream()),
+           "eeg_radial_pack")
+    return img
+
+
+def radial_mlp(f, W0, b0, bh, n_hidden, img, n_out):
+    """-> w_t [n_out/32, E, 32] path-major per-edge tensor-product weights."""
+    E = f.shape[0]
+    w_t = torch.empty(n_out // 32, E, 32, dtype=f32, device=f.device)
+    _begin("eeg_radial_mlp_fwd")
+    _check(lib().eeg_radial_mlp_fwd(_p(f, f32), C.c_int(f.shape[1]), _p(W0, f32), _p(b0, f32), _p(bh, f32), C.c_int(n_hidden),
+                                    C.c_int(W0.shape[0]), _p(img, f32), C.c_int(n_out), _p(w_t), C.c_int64(E), _stream()),
+           "eeg_radial_mlp_fwd")
+    return w_t
+
+
+def tp_scatter(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes):
     M = torch.empty(n_nodes, rows_total * Cch, dtype=f32, device=h.device)
+    E = w_t.shape[1]
     _begin("eeg_tp_scatter_fwd")
     _check(lib().eeg_tp_scatter_fwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]),
-                                    _p(w, f32), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm), _p(M),
-                                    C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_fwd")
+                                    _p(w_t, f32), C.c_int64(E), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm),
+                                    _p(M), C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_fwd")
     return M
 
 

@@ -61,13 +61,26 @@ int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const float* W, 
                          const float* host_scale, const float* bias, int transB, int act, const float* residual,
                          float* out, const EegLayout* lout, int64_t N, void* stream);
 
+/* ---- radial MLP -> per-edge tensor-product weights: `conv_tp_weights` Sequential (gnn/blocks.py:538-549,590) -----
+ * Linear(n_in,64)+SiLU on CUDA cores; n_hidden x [Linear(64,64)+SiLU] and the last Linear(64,n_out,bias=False) on
+ * tcgen05 tensor cores (3xTF32 split, fp32 accumulate in TMEM), weights streamed by the TMA engine (cp.async.bulk).
+ * eeg_radial_pack: one-off (per weight version) repack of Wh [n_hidden,64,64] and W2 [n_out,64] (torch.nn.Linear
+ *   layout) into the staged hi/lo operand image the kernel streams; img has eeg_radial_image_floats() floats.
+ * eeg_radial_mlp_fwd: f [E,n_in] (CSR order), W0 [64,n_in], b0 [64], bh [n_hidden,64], n_out = n_paths*C.
+ *   Output is PATH-MAJOR: w_t [n_out/32][E][32] (tile = path*(C/32) + channel chunk), as eeg_tp_scatter_fwd reads it. */
+int64_t eeg_radial_image_floats(int n_hidden, int n_out);
+int eeg_radial_pack(const float* Wh, int n_hidden, int hidden_dim, const float* W2, int n_out, float* img, void* stream);
+int eeg_radial_mlp_fwd(const float* f, int n_in, const float* W0, const float* b0, const float* bh, int n_hidden,
+                       int hidden_dim, const float* img, int n_out, float* w_t, int64_t E, void* stream);
+
 /* ---- channelwise tensor product + scatter-sum: e3nn TensorProduct 'uvu' + torch_scatter (gnn/blocks.py:591-597)
- * h [N, (lmax_in+1)^2, C] sender features (after linear_up), Y/w/sender in CSR order, w [E, n_paths, C].
+ * h [N, (lmax_in+1)^2, C] sender features (after linear_up); Y / sender in CSR order;
+ * w_t [n_paths * C/32][E][32] PATH-MAJOR per-edge weights in CSR order (eeg_radial_mlp_fwd output).
  * M [N, rows_total, C] with rows laid out per l3 as [(2l3+1), n_paths(l3)] (EegLayout with mul = n_paths*C).
  * (lmax_in, lmax) must be a generated combination: (0,4),(4,4),(0,3),(3,3).  C multiple of 32. */
-int eeg_tp_scatter_fwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w,
-                       const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, float* M, int64_t N,
-                       void* stream);
+int eeg_tp_scatter_fwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
+                       int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, float* M,
+                       int64_t N, void* stream);
 
 /* ---- symmetric contraction (product basis): gnn/mace.py:112-277
  * eeg_sc_coefficients: T[C, n_coef] (channel-major) = (A_csr @ Wflat[n_wrows, C])^T   (A = symmetrised U tensors, built by the host)
