@@ -19,44 +19,62 @@ def sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
-def _digest() -> str:
+def _deps(path: str, seen=None):
+    """The file itself + every quoted #include it reaches (recursively)."""
+    import re
+    seen = set() if seen is None else seen
+    path = os.path.normpath(path)
+    if path in seen or not os.path.exists(path):
+        return seen
+    seen.add(path)
+    with open(path) as f:
+        for inc in re.findall(r'^\s*#\s*include\s+"([^"]+)"', f.read(), flags=re.M):
+            _deps(os.path.join(os.path.dirname(path), inc), seen)
+    return seen
+
+
+def _digest(src: str) -> str:
     h = hashlib.sha256()
-    paths = sources() + [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith(".cuh")]
-    gen = os.path.join(CSRC, "generated")
-    if os.path.isdir(gen):
-        paths += [os.path.join(gen, f) for f in sorted(os.listdir(gen))]
-    paths.append(os.path.join(HERE, "..", "include", "eeg_b200.h"))
-    for p in paths:
+    for p in sorted(_deps(src)):
         with open(p, "rb") as f:
-            h.update(f.read())
+            h.update(p.encode() + b"\0" + f.read())
     h.update(" ".join(FLAGS).encode())
     return h.hexdigest()
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
-    stamp = os.path.join(HERE, "build", "stamp")
-    dig = _digest()
-    if not force and os.path.exists(LIB) and os.path.exists(stamp) and open(stamp).read() == dig:
-        return LIB
-    os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
+    """Incremental: an object is recompiled only when its source, a header it includes, or the flags changed."""
+    bdir = os.path.join(HERE, "build")
+    os.makedirs(bdir, exist_ok=True)
+    srcs = sources()
 
     def cc(src):
-        obj = os.path.join(HERE, "build", os.path.basename(src)[:-3] + ".o")
+        base = os.path.basename(src)[:-3]
+        obj, stamp = os.path.join(bdir, base + ".o"), os.path.join(bdir, base + ".stamp")
+        dig = _digest(src)
+        if not force and not verbose and os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == dig:
+            return obj, False
         cmd = [NVCC, *FLAGS, "-c", src, "-o", obj] + (["-Xptxas", "-v"] if verbose else [])
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
         if verbose:
             sys.stderr.write(r.stderr)
-        return obj
+        with open(stamp, "w") as f:
+            f.write(dig)
+        return obj, True
 
     with cf.ThreadPoolExecutor(max_workers=8) as ex:
-        objs = list(ex.map(cc, sources()))
-    r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-lcudart"], capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    with open(stamp, "w") as f:
-        f.write(dig)
+        res = list(ex.map(cc, srcs))
+    objs = [o for o, _ in res]
+    link_stamp = os.path.join(bdir, "link.stamp")
+    link_key = "\n".join(sorted(objs))
+    if any(ch for _, ch in res) or not os.path.exists(LIB) or not os.path.exists(link_stamp) or open(link_stamp).read() != link_key:
+        r = subprocess.run([NVCC, "-shared", "-o", LIB, *objs, "-lcudart"], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+        with open(link_stamp, "w") as f:
+            f.write(link_key)
     return LIB
 
 

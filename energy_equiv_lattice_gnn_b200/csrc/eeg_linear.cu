@@ -2,6 +2,8 @@
 // Replaces e3nn o3.Linear (einsum 'zui,uw->zwi' per irrep -> cuBLAS bmm; gnn/blocks.py:516-521,552-559,471-476,276-279)
 // and the torch.nn.Linear layers of the radial MLP (gnn/blocks.py:538-549).
 // CUDA-core path: 128x32x16 tiles, 256 threads, 4x4 register micro-tile, float4 smem reads.
+#include <stdlib.h>
+#include <string.h>
 #include "eeg_common.cuh"
 
 namespace {
@@ -138,11 +140,64 @@ __global__ void __launch_bounds__(256) k_block_linear(const float* __restrict__ 
 
 }  // namespace
 
+// tcgen05 path (eeg_tclinear.cu): 0 = launched, -1 = shape outside the tensor-core path, > 0 = error
+int eeg_tc_linear_launch(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off, const float* host_scale,
+                         const float* bias, int transB, const float* residual, float* out, const EegLayout* lout, int64_t N,
+                         int gate, int gate_off, float act_const, const int32_t* in_ld, const int32_t* k_override, cudaStream_t stream);
+
+static bool eeg_linear_use_tc() {
+  static const char* env = getenv("EEG_LINEAR");  // "cuda": force the CUDA-core GEMM (A/B timing, debugging)
+  return !(env && !strcmp(env, "cuda"));
+}
+
+extern "C" int eeg_gate_linear_fwd(const float* z, const EegLayout* lz, int n_scalars, float act_const, const float* W,
+                                   const int64_t* host_w_off, const float* host_scale, float* out, const EegLayout* lout,
+                                   int64_t N, void* stream) {
+  EEG_REQUIRE(lz && lout && lz->n_blocks == lout->n_blocks && lz->n_blocks <= EEG_MAX_L, "eeg_gate_linear_fwd: layout mismatch");
+  if (N == 0) return 0;
+  int32_t in_ld[EEG_MAX_L], kk[EEG_MAX_L];
+  int gates = 0;
+  for (int b = 0; b < lz->n_blocks; ++b) {
+    EEG_REQUIRE(lz->rows[b] == lout->rows[b], "eeg_gate_linear_fwd: block %d rows differ", b);
+    in_ld[b] = lz->mul[b];
+    kk[b] = b == 0 ? n_scalars : lz->mul[b];
+    if (b > 0) {
+      EEG_REQUIRE(lz->mul[b] == lz->mul[1], "eeg_gate_linear_fwd: gated blocks must share one multiplicity");
+      gates += lz->mul[b];
+    }
+  }
+  EEG_REQUIRE(lz->mul[0] == n_scalars + gates, "eeg_gate_linear_fwd: block 0 must hold %d scalars + %d gates", n_scalars, gates);
+  const int rc = eeg_tc_linear_launch(z, lz, W, host_w_off, host_scale, nullptr, 0, nullptr, out, lout, N, 1, n_scalars, act_const,
+                                      in_ld, kk, (cudaStream_t)stream);
+  if (rc == -1) {
+    eeg_set_error("eeg_gate_linear_fwd: shape outside the tensor-core path (multiplicities must be multiples of 32 / 16)");
+    return 3;
+  }
+  return rc;
+}
+
 extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off,
                                     const float* host_scale, const float* bias, int transB, int act, const float* residual,
                                     float* out, const EegLayout* lout, int64_t N, void* stream) {
   EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_fwd: layout mismatch");
   if (N == 0) return 0;
+  if (act == 0 && eeg_linear_use_tc()) {
+    // Measured on B200 (N = 30720): the tensor-core kernel wins for the path-stacked interaction.linear (K = 160..320:
+    // 393 us vs 478 us) but not yet for the K = 32 mixes (140-250 us vs 80-100 us: its LDG/STS-staged producers and the
+    // epilogue share one congested memory-instruction queue), so short-K shapes stay on the CUDA-core GEMM.
+    bool same_rows = true;
+    int max_k = 0;
+    for (int b = 0; b < lin->n_blocks; ++b) {
+      same_rows &= lin->rows[b] == lout->rows[b];
+      if (lin->mul[b] > max_k) max_k = lin->mul[b];
+    }
+    static const char* env = getenv("EEG_LINEAR");
+    if (same_rows && (max_k >= 128 || (env && !strcmp(env, "tc")))) {
+      const int rc = eeg_tc_linear_launch(in, lin, W, host_w_off, host_scale, bias, transB, residual, out, lout, N, 0, 0, 0.f,
+                                          nullptr, nullptr, (cudaStream_t)stream);
+      if (rc != -1) return rc;
+    }
+  }
   LinearParams P;
   P.n_blocks = lin->n_blocks;
   P.in_stride = lin->stride;

@@ -262,11 +262,16 @@ class EnergyEquivGNN(torch.nn.Module):
         w1off = [0] + [C * (C + n_gates) + b * C * C for b in range(lmax)]
         nv.set_tag('readout.linear_1')
         z = nv.block_linear(h, self._lay_h, ro.linear_1.weight.detach(), w1off, [sC] * (lmax + 1), self._lay_z, N)
-        nv.set_tag('readout.gate')
-        g = nv.gate(z, self._lay_z, self._lay_g, C, NORM2MOM_SILU, N)
         w2off = np.concatenate(([0], np.cumsum([C * m for m in self.rmul])))[:-1].tolist()
-        nv.set_tag('readout.linear_2')
-        o = nv.block_linear(g, self._lay_g, ro.linear_2.weight.detach(), w2off, [sC] * (lmax + 1), self._lay_o, N)
+        g = o = None
+        if save is None:  # inference: Gate applied while linear_2's operand rows are staged (no gated tensor in HBM)
+            nv.set_tag('readout.gate_linear_2')
+            o = nv.gate_linear(z, self._lay_z, C, NORM2MOM_SILU, ro.linear_2.weight.detach(), w2off, [sC] * (lmax + 1), self._lay_o, N)
+        if o is None:
+            nv.set_tag('readout.gate')
+            g = nv.gate(z, self._lay_z, self._lay_g, C, NORM2MOM_SILU, N)
+            nv.set_tag('readout.linear_2')
+            o = nv.block_linear(g, self._lay_g, ro.linear_2.weight.detach(), w2off, [sC] * (lmax + 1), self._lay_o, N)
         qscale = [1.0 / math.sqrt(m) for m in self.rmul]
         nv.set_tag('pool_tail')
         Cst, q, A = nv.pool_tail(o, self._lay_o, gp, head.linear.weight.detach(), self._qmul, qscale, head.linear.bias.detach(),

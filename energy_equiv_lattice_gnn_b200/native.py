@@ -17,7 +17,7 @@ EEG_MAX_L = 8
 
 SYMBOLS = [
     "eeg_last_error", "eeg_abi_version", "eeg_csr_workspace_bytes", "eeg_csr_build", "eeg_graph_ptr",
-    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
+    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_gate_linear_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
     "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd", "eeg_radial_image_floats", "eeg_radial_pack", "eeg_radial_mlp_fwd",
 ]
 
@@ -62,7 +62,7 @@ def lib() -> C.CDLL:
 # Optional per-entry-point CUDA-event timing (bench.py roofline leg) and launch accounting.
 # KERNELS_PER_CALL = kernels one C-ABI call launches (memsets excluded).
 KERNELS_PER_CALL = {"eeg_csr_build": 6, "eeg_graph_ptr": 1, "eeg_node_embed_fwd": 1, "eeg_edge_featurize": 1,
-                    "eeg_block_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
+                    "eeg_block_linear_fwd": 1, "eeg_gate_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
                     "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1,
                     "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1}
 launch_count = 0
@@ -184,6 +184,21 @@ def block_linear(x, lin: EegLayout, W, w_off: Sequence[int], scale: Sequence[flo
     _check(lib().eeg_block_linear_fwd(_p(x, f32), C.byref(lin), _p(W, f32), woff, sc, _p(bias, f32), C.c_int(int(transB)),
                                       C.c_int(act), _p(residual, f32), _p(out, f32), C.byref(lout), C.c_int64(n_rows),
                                       _stream()), "eeg_block_linear_fwd")
+    return out
+
+
+def gate_linear(z, lz: EegLayout, n_scalars: int, act_const: float, W, w_off: Sequence[int], scale: Sequence[float],
+                lout: EegLayout, n_rows: int):
+    """Gate fused into the following o3.Linear (tensor-core path). Returns None when the shape is not supported."""
+    nb = lz.n_blocks
+    if any(lz.mul[b] % 32 for b in range(nb)) or n_scalars % 32 or any(lout.mul[b] % 16 for b in range(nb)):
+        return None
+    out = torch.empty(n_rows, lout.stride, dtype=f32, device=z.device)
+    woff = (C.c_int64 * EEG_MAX_L)(*list(w_off) + [0] * (EEG_MAX_L - nb))
+    sc = (C.c_float * EEG_MAX_L)(*list(scale) + [0.0] * (EEG_MAX_L - nb))
+    _begin("eeg_gate_linear_fwd")
+    _check(lib().eeg_gate_linear_fwd(_p(z, f32), C.byref(lz), C.c_int(n_scalars), C.c_float(act_const), _p(W, f32), woff, sc,
+                                     _p(out, f32), C.byref(lout), C.c_int64(n_rows), _stream()), "eeg_gate_linear_fwd")
     return out
 
 

@@ -4,7 +4,8 @@
                 sqrt(2 l3 + 1) path coefficient folded in (gnn/mace.py:286-314, gnn/blocks.py:528-535).
 * `sc_plan`   - symmetric-contraction "program": the generalised CG tensors of gnn/mace.py:435-477 symmetrised over
                 input permutations and ordered for Horner evaluation
-                    out_M = sum_i x_i (T1[M,i] + sum_{j>=i} x_j (T2[M,i,j] + sum_{t>=j} T3[M,i,j,t] x_t)).
+                    out_M = sum_i x_i (T1[M,i] + sum_j x_j (T2[M,i,j] + sum_t T3[M,i,j,t] x_t))
+                (which two indices of a monomial sit on the outer levels is chosen greedily, see _factorise).
                 Every coefficient T is a fixed linear combination of the trainable weights W_nu^L[k, c]; the plan
                 carries that map as a sparse matrix (row = coefficient slot in consumption order).
 """
@@ -57,6 +58,69 @@ def _sym_entries(lmax: int, nu: int, L: int):
     return out, k
 
 
+def _factorise(M: int, ent, correlation: int):
+    """Horner tree {outer i: {middle j: set(inner t)}} for output component M.
+
+    A symmetrised monomial x_a x_b x_c may put ANY two of its indices on the (outer, middle) levels.  The evaluation
+    costs one multiply-add per coefficient, one per distinct (outer, middle) pair and one per distinct outer index, so
+    pairs are chosen greedily by how many still-unassigned monomials they cover (pairs that carry a degree-2
+    coefficient exist anyway and are used first).  For lmax = 4 this needs 2.2 k pairs instead of the 4.3 k of the
+    fixed i <= j <= t nesting."""
+    import collections
+    import itertools
+    monos = [kk[1:] for kk in ent.get(3, {}) if kk[0] == M] if correlation >= 3 else []
+    pairs = [kk[1:] for kk in ent.get(2, {}) if kk[0] == M] if correlation >= 2 else []  # sorted (a, b)
+
+    def pairs_of(m):
+        return sorted({tuple(sorted(p)) for p in itertools.combinations(m, 2)})
+
+    chosen = list(sorted(pairs))
+    cover = {}
+    have = set(chosen)
+    left = []
+    for m in sorted(monos):
+        hit = [p for p in pairs_of(m) if p in have]
+        if hit:
+            cover[m] = hit[0]
+        else:
+            left.append(m)
+    while left:
+        cnt = collections.Counter()
+        for m in left:
+            for p in pairs_of(m):
+                cnt[p] += 1
+        best = max(cnt.items(), key=lambda kv: (kv[1], tuple(-a for a in kv[0])))[0]
+        chosen.append(best)
+        nxt = []
+        for m in left:
+            if best in pairs_of(m):
+                cover[m] = best
+            else:
+                nxt.append(m)
+        left = nxt
+    # orientation: the index that occurs in more pairs goes outside (fewer distinct outer indices)
+    freq = collections.Counter(a for p in chosen for a in set(p))
+    for (m, i) in (kk for kk in ent[1] if kk[0] == M):
+        freq[i] += 1000  # an outer level that exists anyway (degree-1 coefficient)
+    orient = {}
+    for p in chosen:
+        a, b = p
+        orient[p] = (a, b) if (freq[a], -a) >= (freq[b], -b) else (b, a)
+    tree = {}
+    for (m, i) in (kk for kk in ent[1] if kk[0] == M):
+        tree.setdefault(i, {})
+    for p in chosen:
+        o, mid = orient[p]
+        tree.setdefault(o, {}).setdefault(mid, set())
+    for m, p in cover.items():
+        rest = list(m)
+        rest.remove(p[0])
+        rest.remove(p[1])
+        o, mid = orient[p]
+        tree[o][mid].add(rest[0])
+    return tree
+
+
 @functools.lru_cache(maxsize=None)
 def sc_plan(lmax: int, correlation: int):
     """Horner program + coefficient->weight map for all output irreps L = 0..lmax.
@@ -79,17 +143,7 @@ def sc_plan(lmax: int, correlation: int):
             wshape[(L, nu)] = k
         ops_L = []
         for M in range(2 * L + 1):
-            tree: Dict[int, Dict] = {}
-            for (m, i), _ in ((kk, 0) for kk in ent[1] if kk[0] == M):
-                tree.setdefault(i, {})
-            if correlation >= 2:
-                for kk in ent[2]:
-                    if kk[0] == M:
-                        tree.setdefault(kk[1], {}).setdefault(kk[2], set())
-            if correlation >= 3:
-                for kk in ent[3]:
-                    if kk[0] == M:
-                        tree.setdefault(kk[1], {}).setdefault(kk[2], set()).add(kk[3])
+            tree = _factorise(M, ent, correlation)
             ops_M = []
             for i in sorted(tree):
                 c1 = -1
@@ -100,13 +154,15 @@ def sc_plan(lmax: int, correlation: int):
                 js = []
                 for j in sorted(tree[i]):
                     c2 = -1
-                    if correlation >= 2 and (M, i, j) in ent[2]:
+                    k2 = (M,) + tuple(sorted((i, j)))
+                    if correlation >= 2 and k2 in ent[2]:
                         c2 = slot
-                        A += [(slot, L, 2, kq, float(v)) for kq, v in enumerate(ent[2][(M, i, j)]) if abs(v) > 1e-12]
+                        A += [(slot, L, 2, kq, float(v)) for kq, v in enumerate(ent[2][k2]) if abs(v) > 1e-12]
                         slot += 1
                     ts = []
                     for t in sorted(tree[i][j]):
-                        A += [(slot, L, 3, kq, float(v)) for kq, v in enumerate(ent[3][(M, i, j, t)]) if abs(v) > 1e-12]
+                        k3 = (M,) + tuple(sorted((i, j, t)))
+                        A += [(slot, L, 3, kq, float(v)) for kq, v in enumerate(ent[3][k3]) if abs(v) > 1e-12]
                         ts.append((t, slot))
                         slot += 1
                     js.append((j, c2, ts))

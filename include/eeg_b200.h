@@ -61,6 +61,19 @@ int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const float* W, 
                          const float* host_scale, const float* bias, int transB, int act, const float* residual,
                          float* out, const EegLayout* lout, int64_t N, void* stream);
 
+/* Shapes with every mul_in a multiple of 32 and mul_out a multiple of 16 (act == 0) run on the tcgen05 tensor cores
+ * (3xTF32 split, fp32 accumulation in TMEM; eeg_tclinear.cu); anything else on the CUDA-core GEMM.  Same results to
+ * fp32 round-off.  EEG_LINEAR=cuda in the environment forces the CUDA-core path. */
+
+/* ---- e3nn.nn.Gate (gnn/blocks.py:268-282) fused into the following o3.Linear (readout linear_2, gnn/blocks.py:276-283):
+ * z layout lz: block 0 = [n_scalars scalars | gates of block 1 | gates of block 2 ...], blocks b >= 1 = gated features.
+ * out[n,b,m,w] = scale[b] * sum_u g[n,b,m,u] W_b[u,w],  g_0 = c*silu(scalars),  g_b = z_b * c*silu(gates_b).
+ * Tensor-core path only (mul multiples of 32, mul_out multiples of 16); returns 3 when the shape is not supported so
+ * the caller can run eeg_gate_fwd + eeg_block_linear_fwd instead. */
+int eeg_gate_linear_fwd(const float* z, const EegLayout* lz, int n_scalars, float act_const, const float* W,
+                        const int64_t* host_w_off, const float* host_scale, float* out, const EegLayout* lout, int64_t N,
+                        void* stream);
+
 /* ---- radial MLP -> per-edge tensor-product weights: `conv_tp_weights` Sequential (gnn/blocks.py:538-549,590) -----
  * Linear(n_in,64)+SiLU on CUDA cores; n_hidden x [Linear(64,64)+SiLU] and the last Linear(64,n_out,bias=False) on
  * tcgen05 tensor cores (3xTF32 split, fp32 accumulate in TMEM), weights streamed by the TMA engine (cp.async.bulk).

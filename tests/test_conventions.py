@@ -129,6 +129,49 @@ def test_sc_plan_counts():
     assert wm["n_wrows"] == sum(plan["wshape"].values()) and wm["row_ptr"][-1] == len(wm["col"])
 
 
+@pytest.mark.parametrize("lmax", [2, 3])
+def test_sc_plan_equals_reference_contraction(lmax):
+    """The Horner program (whatever factorisation _factorise picks) + the weight map reproduce the reference's
+    U.W.x contraction (gnn/mace.py:261-277, restated in oracle/model.py) on random inputs, in fp64."""
+    import torch
+    from oracle.model import SymmetricContraction
+    torch.manual_seed(0)
+    nu, C, B = 3, 3, 4
+    D = (lmax + 1) ** 2
+    irreps = [(C, L, (-1) ** L) for L in range(lmax + 1)]
+    sc = SymmetricContraction(lmax, irreps, nu, C).double()
+    x = torch.randn(B, C, D, dtype=torch.float64)
+    ref = sc(x).detach()  # [B, sum_L C*(2L+1)], c-major per L
+    plan, wm = tb.sc_plan(lmax, nu), tb.sc_weight_map(lmax, nu)
+    Wflat = torch.cat([sc.contractions[k].weights[str(n)].detach() for k in sc.keys for n in range(1, nu + 1)], 0).numpy()
+    A = np.zeros((wm["n_coef"], wm["n_wrows"]))
+    for r in range(wm["n_coef"]):
+        for q in range(wm["row_ptr"][r], wm["row_ptr"][r + 1]):
+            A[r, wm["col"][q]] += wm["val"][q]
+    T = A @ Wflat  # [n_coef, C]
+    xn = x.numpy()
+    got = np.zeros((B, C, D))
+    o = 0
+    for ops_L in plan["ops"]:
+        for ops_M in ops_L:
+            acc = np.zeros((B, C))
+            for i, c1, js in ops_M:
+                m1 = np.zeros((B, C)) + (T[c1] if c1 >= 0 else 0.0)
+                for j, c2, ts in js:
+                    m2 = np.zeros((B, C)) + (T[c2] if c2 >= 0 else 0.0)
+                    for t, c3 in ts:
+                        m2 = m2 + T[c3] * xn[:, :, t]
+                    m1 = m1 + m2 * xn[:, :, j]
+                acc = acc + m1 * xn[:, :, i]
+            got[:, :, o] = acc
+            o += 1
+    off, refs = 0, []
+    for L in range(lmax + 1):
+        refs.append(ref[:, off:off + C * (2 * L + 1)].reshape(B, C, 2 * L + 1).numpy())
+        off += C * (2 * L + 1)
+    assert np.allclose(got, np.concatenate(refs, -1), rtol=1e-6, atol=1e-6)  # map values are stored in fp32
+
+
 @pytest.mark.parametrize("s,want", [("32x0e+32x1o", [(32, 0, 1), (32, 1, -1)]), ("2x0e+2x2e+1x4e", [(2, 0, 1), (2, 2, 1), (1, 4, 1)])])
 def test_parse_irreps(s, want):
     assert cv.parse_irreps(s) == want and cv.irreps_str(want) == s

@@ -55,8 +55,113 @@ def check_radial(E=122880, n_out=1344, n_hidden=1, n_in=12, seed=0):
     return err
 
 
+def check_sc(N=30720, C=32, lmax=4):
+    """Times the symmetric-contraction variant selected by EEG_SC_VARIANT; dumps a slice for cross-variant comparison."""
+    from energy_equiv_lattice_gnn_b200 import tables as tb
+    n_coef = tb.sc_plan(lmax, 3)["n_coef"]
+    D = (lmax + 1) ** 2
+    g = torch.Generator().manual_seed(1)
+    T = (0.1 * torch.randn(C, n_coef, generator=g)).to(dev)
+    x = torch.randn(N, D, C, generator=g).to(dev)
+    out = nv.sym_contract(lmax, 3, C, x, T, N)
+    torch.cuda.synchronize()
+    ms = timeit(lambda: nv.sym_contract(lmax, 3, C, x, T, N), n=10)
+    v = os.environ.get("EEG_SC_VARIANT", "default")
+    os.makedirs("gpurun_out", exist_ok=True)
+    torch.save(torch.cat([out[:300], out[-300:]]).cpu(), f"gpurun_out/sc_{v}_l{lmax}.pt")
+    print(f"sc variant={v} lmax={lmax} N={N} C={C}: {ms*1e3:.1f} us  checksum {float(out.double().sum()):.9e}", flush=True)
+
+
+def check_linear(N=30720, C=32, lmax=4, npaths=(5, 8, 10, 10, 9), seed=0):
+    """Block linears (tcgen05 3xTF32 unless EEG_LINEAR=cuda) vs torch fp64: the a14 shape, a 32->32 mix with residual,
+    linear_1 (0e block 32->160) and the gate-fused linear_2."""
+    g = torch.Generator().manual_seed(seed)
+    rows = [2 * l + 1 for l in range(lmax + 1)]
+    ok = True
+
+    def run(name, lin, lout, W, woff, scale, x, bias=None, residual=None, ragged_rows=None):
+        nonlocal ok
+        n = x.shape[0]
+        out = nv.block_linear(x, lin, W, woff, scale, lout, n, bias=bias, residual=residual)
+        torch.cuda.synchronize()
+        ref = torch.zeros(n, lout.stride, dtype=torch.float64)
+        xd, Wd = x.double().cpu(), W.double().cpu()
+        for b in range(lin.n_blocks):
+            k, no, r = lin.mul[b], lout.mul[b], lin.rows[b]
+            xb = xd[:, lin.off[b]:lin.off[b] + r * k].reshape(n, r, k)
+            Wb = Wd[woff[b]:woff[b] + k * no].reshape(k, no)
+            yb = scale[b] * xb @ Wb
+            if bias is not None and b == 0:
+                yb = yb + bias.double().cpu()
+            ref[:, lout.off[b]:lout.off[b] + r * no] = yb.reshape(n, r * no)
+        if residual is not None:
+            ref += residual.double().cpu()
+        err = float((out.double().cpu() - ref).abs().max() / ref.abs().max())
+        ms = timeit(lambda: nv.block_linear(x, lin, W, woff, scale, lout, n, bias=bias, residual=residual), n=10)
+        gb = (x.numel() + out.numel() + (residual.numel() if residual is not None else 0)) * 4 / 1e9
+        print(f"linear {name:18s} N={n}: rel err {err:.2e}  {ms*1e3:7.1f} us  {gb/ms*1e3:6.0f} GB/s", flush=True)
+        ok &= err < 4e-6
+
+    for n in (N, 1000, 77):
+        # a14: path-stacked messages -> hidden
+        lin = nv.make_layout(rows, [p * C for p in npaths]); lout = nv.make_layout(rows, [C] * (lmax + 1))
+        woff = [0]
+        for p in npaths[:-1]:
+            woff.append(woff[-1] + p * C * C)
+        W = torch.randn(sum(p * C * C for p in npaths), generator=g).to(dev)
+        x = torch.randn(n, lin.stride, generator=g).to(dev)
+        run("interaction(a14)", lin, lout, W, woff, [1.0 / (p * C) ** 0.5 for p in npaths], x, bias=torch.randn(C, generator=g).to(dev))
+        # 32 -> 32 with residual
+        lin = nv.make_layout(rows, [C] * (lmax + 1))
+        W = torch.randn((lmax + 1) * C * C, generator=g).to(dev)
+        x = torch.randn(n, lin.stride, generator=g).to(dev)
+        res = torch.randn(n, lin.stride, generator=g).to(dev)
+        run("product+residual", lin, lin, W, [b * C * C for b in range(lmax + 1)], [C ** -0.5] * (lmax + 1), x, residual=res)
+        # linear_1: 0e block -> C + lmax*C
+        lz = nv.make_layout(rows, [C + lmax * C] + [C] * lmax)
+        W = torch.randn(C * (C + lmax * C) + lmax * C * C, generator=g).to(dev)
+        w1off = [0] + [C * (C + lmax * C) + b * C * C for b in range(lmax)]
+        run("readout.linear_1", lin, lz, W, w1off, [C ** -0.5] * (lmax + 1), x)
+        # gate fused into linear_2 (C -> C/2)
+        lo = nv.make_layout(rows, [C // 2] * (lmax + 1)); lg = nv.make_layout(rows, [C] * (lmax + 1))
+        z = torch.randn(n, lz.stride, generator=g).to(dev)
+        W2 = torch.randn((lmax + 1) * C * (C // 2), generator=g).to(dev)
+        w2off = [b * C * (C // 2) for b in range(lmax + 1)]
+        cst = 1.6791767923989418
+        o = nv.gate_linear(z, lz, C, cst, W2, w2off, [C ** -0.5] * (lmax + 1), lo, n)
+        torch.cuda.synchronize()
+        zd = z.double().cpu()
+        sil = lambda t: t / (1 + torch.exp(-t))  # noqa: E731
+        ref = torch.zeros(n, lo.stride, dtype=torch.float64)
+        for b in range(lmax + 1):
+            r = rows[b]
+            if b == 0:
+                gb_ = cst * sil(zd[:, :C]).reshape(n, 1, C)
+            else:
+                gate = cst * sil(zd[:, C + C * (b - 1):C + C * b])
+                gb_ = zd[:, lz.off[b]:lz.off[b] + r * C].reshape(n, r, C) * gate[:, None, :]
+            ref[:, lo.off[b]:lo.off[b] + r * (C // 2)] = (C ** -0.5 * gb_ @ W2.double().cpu()[w2off[b]:w2off[b] + C * C // 2].reshape(C, C // 2)).reshape(n, -1)
+        err = float((o.double().cpu() - ref).abs().max() / ref.abs().max())
+        ms = timeit(lambda: nv.gate_linear(z, lz, C, cst, W2, w2off, [C ** -0.5] * (lmax + 1), lo, n), n=10)
+        print(f"linear {'gate+linear_2':18s} N={n}: rel err {err:.2e}  {ms*1e3:7.1f} us  {(z.numel()+o.numel())*4/1e9/ms*1e3:6.0f} GB/s", flush=True)
+        ok &= err < 4e-6
+    print("LINEAR", "OK" if ok else "FAIL", "(EEG_LINEAR=%s)" % os.environ.get("EEG_LINEAR", "tc"))
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "radial"
+    if what == "linear":
+        check_linear()
+    if what == "sc":
+        check_sc(int(sys.argv[2]) if len(sys.argv) > 2 else 30720, 32, int(sys.argv[3]) if len(sys.argv) > 3 else 4)
+    if what == "sc_compare":
+        import glob
+        for lmax in (3, 4):
+            fs = sorted(glob.glob(f"gpurun_out/sc_*_l{lmax}.pt"))
+            if fs:
+                ref = torch.load(fs[0])
+                for f in fs[1:]:
+                    print(f"{f} vs {fs[0]}: max abs diff {float((torch.load(f) - ref).abs().max()):.3e}")
     if what == "radial":
         if len(sys.argv) > 2:
             check_radial(int(sys.argv[2]), int(sys.argv[3]) if len(sys.argv) > 3 else 1344)
