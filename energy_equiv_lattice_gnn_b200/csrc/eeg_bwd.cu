@@ -1,0 +1,452 @@
+// Explicit backward kernels of the readout / tail / linear stages (the reference relies on autograd over e3nn ops):
+//   eeg_block_linear_wgrad : dW_b[u,w] += scale_b sum_{n,m} x[n,b,m,u] dy[n,b,m,w]  (+ bias gradient on the 0e block)
+//   eeg_colsum             : out[c] += sum_r a[r] x[r,c]   (bias gradients of the radial MLP, embedding gradients)
+//   eeg_silu_fwd / _bwd    : SiLU of the radial MLP (gnn/blocks.py:538-549), recomputed in the backward pass
+//   eeg_gate_bwd           : e3nn.nn.Gate backward (gnn/blocks.py:268-282)
+//   eeg_pool_tail_bwd      : PositiveLayer, Cart_4_to_Mandel, Spherical_to_Cartesian, final o3.Linear and graph pooling
+//                            (gnn/model.py:100-111, gnn/blocks.py:185-229,392-442) + eeg_tail_wgrad for its weights
+// The input-gradient of a linear is eeg_block_linear_fwd with transB = 1 (dX = dY W^T).
+#include <math.h>
+#include "eeg_common.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------ linear weight gradient
+constexpr int WG_ROWS = 4096;   // rows per CTA
+
+struct WgBlock {
+  int rows, k, nout, in_off, in_ld, out_off;
+  int64_t w_off;
+  float scale;
+  int cta_begin, ktiles, ntiles;
+};
+struct WgParams {
+  WgBlock b[EEG_MAX_L];
+  int n_blocks, in_stride, out_stride, transB;
+};
+
+__global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dW,
+                                                      float* __restrict__ dbias, int64_t N, WgParams P) {
+  __shared__ __align__(16) float Xs[32][36];
+  __shared__ __align__(16) float Ys[32][36];
+  int cta = blockIdx.x, bi = 0;
+#pragma unroll
+  for (int q = 1; q < EEG_MAX_L; ++q)
+    if (q < P.n_blocks && cta >= P.b[q].cta_begin) bi = q;
+  const WgBlock d = P.b[bi];
+  cta -= d.cta_begin;
+  const int tiles = d.ktiles * d.ntiles;
+  const int kt = (cta % tiles) / d.ntiles, nt = (cta % tiles) % d.ntiles;
+  const int64_t r_begin = (int64_t)(cta / tiles) * WG_ROWS, total = N * d.rows;
+  const int64_t r_end = r_begin + WG_ROWS < total ? r_begin + WG_ROWS : total;
+  const int t = threadIdx.x, tk = t >> 3, tn = t & 7;   // thread: k = 2 tk + {0,1}, n = 4 tn + {0..3}
+  const int lr = t >> 2, lq = t & 3;                     // loader: row lr, float4 columns lq and lq + 4
+  float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+  float bsum[4] = {0.f, 0.f, 0.f, 0.f};
+  const bool want_bias = dbias != nullptr && bi == 0 && kt == 0 && tk == 0;
+  for (int64_t r0 = r_begin; r0 < r_end; r0 += 32) {
+    const int64_t r = r0 + lr;
+    const bool ok = r < r_end;
+    const int64_t n = ok ? r / d.rows : 0;
+    const int m = ok ? (int)(r - n * d.rows) : 0;
+    const float* xr = x + n * P.in_stride + d.in_off + (int64_t)m * d.in_ld + kt * 32;
+    const float* yr = dy + n * P.out_stride + d.out_off + (int64_t)m * d.nout + nt * 32;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int c4 = (lq + 4 * h) * 4;
+      float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), yv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok && kt * 32 + c4 < d.k) xv = __ldg(reinterpret_cast<const float4*>(xr + c4));
+      if (ok && nt * 32 + c4 < d.nout) yv = __ldg(reinterpret_cast<const float4*>(yr + c4));
+      *reinterpret_cast<float4*>(&Xs[lr][c4]) = xv;
+      *reinterpret_cast<float4*>(&Ys[lr][c4]) = yv;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int rr = 0; rr < 32; ++rr) {
+      const float2 a = *reinterpret_cast<const float2*>(&Xs[rr][2 * tk]);
+      const float4 b = *reinterpret_cast<const float4*>(&Ys[rr][4 * tn]);
+      acc[0][0] = fmaf(a.x, b.x, acc[0][0]); acc[0][1] = fmaf(a.x, b.y, acc[0][1]);
+      acc[0][2] = fmaf(a.x, b.z, acc[0][2]); acc[0][3] = fmaf(a.x, b.w, acc[0][3]);
+      acc[1][0] = fmaf(a.y, b.x, acc[1][0]); acc[1][1] = fmaf(a.y, b.y, acc[1][1]);
+      acc[1][2] = fmaf(a.y, b.z, acc[1][2]); acc[1][3] = fmaf(a.y, b.w, acc[1][3]);
+      if (want_bias) { bsum[0] += b.x; bsum[1] += b.y; bsum[2] += b.z; bsum[3] += b.w; }
+    }
+    __syncthreads();
+  }
+  float* Wb = dW + d.w_off;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = kt * 32 + 2 * tk + i, n = nt * 32 + 4 * tn + j;
+      if (k < d.k && n < d.nout) atomicAdd(Wb + (P.transB ? (int64_t)n * d.k + k : (int64_t)k * d.nout + n), acc[i][j] * d.scale);
+    }
+  if (want_bias)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (nt * 32 + 4 * tn + j < d.nout) atomicAdd(dbias + nt * 32 + 4 * tn + j, bsum[j]);
+}
+
+// ------------------------------------------------------------------------------------------------ column sums
+__global__ void k_colsum(const float* __restrict__ x, int64_t R, int ld, int cols, const float* __restrict__ a, float* __restrict__ out,
+                         int rows_per_cta) {
+  const int c = blockIdx.y * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta, r1 = r0 + rows_per_cta < R ? r0 + rows_per_cta : R;
+  float s = 0.f;
+  for (int64_t r = r0; r < r1; ++r) s = fmaf(a ? __ldg(a + r) : 1.0f, __ldg(x + r * ld + c), s);
+  atomicAdd(out + c, s);
+}
+
+__global__ void k_silu_fwd(const float* __restrict__ a, float* __restrict__ s, int64_t n) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) s[i] = eeg_silu(a[i]);
+}
+__device__ __forceinline__ float silu_grad(float x) {
+  const float sg = 1.0f / (1.0f + __expf(-x));
+  return sg * (1.0f + x * (1.0f - sg));
+}
+__global__ void k_silu_bwd(const float* __restrict__ a, const float* __restrict__ ds, float* __restrict__ da, int64_t n) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) da[i] = ds[i] * silu_grad(a[i]);
+}
+
+// ------------------------------------------------------------------------------------------------ gate backward
+struct GateBwdParams {
+  EegLayout lz, lg;
+  int gate_off[EEG_MAX_L];
+  int n_scalars;
+  float c;
+};
+__global__ void k_gate_bwd(const float* __restrict__ z, const float* __restrict__ dg, float* __restrict__ dz, GateBwdParams P) {
+  const int64_t n = blockIdx.x;
+  const float* zr = z + n * P.lz.stride;
+  const float* gr = dg + n * P.lg.stride;
+  float* dr = dz + n * P.lz.stride;
+  for (int u = threadIdx.x; u < P.n_scalars; u += blockDim.x) dr[u] = gr[u] * P.c * silu_grad(zr[u]);
+  for (int b = 1; b < P.lz.n_blocks; ++b) {
+    const int mul = P.lz.mul[b], rows = P.lz.rows[b];
+    for (int u = threadIdx.x; u < mul; u += blockDim.x) {
+      const float zg = zr[P.gate_off[b] + u];
+      const float gv = P.c * eeg_silu(zg);
+      float s = 0.f;
+      for (int m = 0; m < rows; ++m) {
+        const float d = gr[P.lg.off[b] + m * mul + u];
+        s = fmaf(d, zr[P.lz.off[b] + m * mul + u], s);
+        dr[P.lz.off[b] + m * mul + u] = d * gv;
+      }
+      dr[P.gate_off[b] + u] = s * P.c * silu_grad(zg);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ tail backward
+struct TailBwdParams {
+  EegLayout lo;
+  int qmul[EEG_MAX_L], qoff[EEG_MAX_L], woff[EEG_MAX_L], poff[EEG_MAX_L];
+  float qscale[EEG_MAX_L];
+  int nq, npool, positive, reduce;
+};
+__device__ __forceinline__ void mat6_sq_bwd(const float* A, const float* dC, float* dA, int t) {  // C = A A: dA = dC A^T + A^T dC
+  if (t < 36) {
+    const int r = t / 6, c = t % 6;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s += dC[r * 6 + k] * A[c * 6 + k] + A[k * 6 + r] * dC[k * 6 + c];
+    dA[t] = s;
+  }
+}
+__device__ __forceinline__ void mat6_mul_b(const float* A, const float* B, float* Cm, int t) {
+  if (t < 36) {
+    const int r = t / 6, c = t % 6;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s = fmaf(A[r * 6 + k], B[k * 6 + c], s);
+    Cm[t] = s;
+  }
+}
+__global__ void __launch_bounds__(128) k_pool_tail_bwd(const float* __restrict__ o, const int32_t* __restrict__ gp,
+                                                       const float* __restrict__ Wq, const float* __restrict__ Pm,
+                                                       const float* __restrict__ A_in, const float* __restrict__ dC,
+                                                       float* __restrict__ d_o, float* __restrict__ dq_out,
+                                                       float* __restrict__ pooled_out, TailBwdParams P) {
+  extern __shared__ float sm[];
+  float* dpool = sm;            // [npool]
+  float* dq = dpool + P.npool;  // [nq]
+  float* A = dq + P.nq;         // 5 x [36]
+  float* B = A + 36;
+  float* dCs = B + 36;
+  float* dB = dCs + 36;
+  float* dA = dB + 36;
+  const int g = blockIdx.x, t = threadIdx.x;
+  const int nb = gp[g], ne = gp[g + 1];
+  const float inv = (P.reduce == 0) ? 1.0f / (float)max(ne - nb, 1) : 1.0f;
+  if (t < 36) {
+    A[t] = A_in[(int64_t)g * 36 + t];
+    dCs[t] = dC[(int64_t)g * 36 + t];
+  }
+  __syncthreads();
+  if (P.positive == 0) {
+    if (t < 36) dA[t] = dCs[t];
+  } else if (P.positive == 1) {
+    mat6_sq_bwd(A, dCs, dA, t);
+  } else {
+    float post = 1.f;
+    if (P.positive == 3 || P.positive == 4) {
+      const float kk = (P.positive == 3) ? 2.f : 4.f;
+      if (t < 36) A[t] = A[t] / kk + ((t / 6 == t % 6) ? 1.f : 0.f);
+      post = 1.f / kk;
+      __syncthreads();
+    }
+    if (P.positive == 3) {
+      mat6_sq_bwd(A, dCs, dA, t);
+    } else {  // fourth power: B = A^2, C = B^2
+      mat6_mul_b(A, A, B, t);
+      __syncthreads();
+      mat6_sq_bwd(B, dCs, dB, t);
+      __syncthreads();
+      mat6_sq_bwd(A, dB, dA, t);
+    }
+    __syncthreads();
+    if (t < 36) dA[t] *= post;
+  }
+  __syncthreads();
+  for (int k = t; k < P.nq; k += blockDim.x) {
+    float s = 0.f;
+    for (int e = 0; e < 36; ++e) s = fmaf(__ldg(Pm + k * 36 + e), dA[e], s);
+    dq[k] = s;
+    dq_out[(int64_t)g * P.nq + k] = s;
+  }
+  __syncthreads();
+  // d pooled_b[m][u] = scale_b sum_w dq[b][w][m] W_b[u][w];  pooled itself is re-reduced for the weight gradient
+  for (int i = t; i < P.npool; i += blockDim.x) {
+    int b = -1;
+    for (int k = 0; k < P.lo.n_blocks; ++k)
+      if (P.qmul[k] > 0 && i >= P.poff[k]) b = k;
+    const int rows = P.lo.rows[b], mul = P.lo.mul[b], r = i - P.poff[b];
+    const int m = r / mul, u = r % mul;
+    float s = 0.f;
+    for (int w = 0; w < P.qmul[b]; ++w) s = fmaf(dq[P.qoff[b] + w * rows + m], __ldg(Wq + P.woff[b] + u * P.qmul[b] + w), s);
+    dpool[i] = s * P.qscale[b] * inv;
+    const float* src = o + (int64_t)nb * P.lo.stride + P.lo.off[b] + r;
+    float ps = 0.f;
+    for (int n = nb; n < ne; ++n, src += P.lo.stride) ps += __ldg(src);
+    pooled_out[(int64_t)g * P.npool + i] = ps * inv;
+  }
+  __syncthreads();
+  // d o[n] = d pooled / count for the pooled blocks, zero for the blocks the final linear ignores
+  for (int i = t; i < P.lo.stride; i += blockDim.x) {
+    int b = 0;
+    for (int k = 1; k < P.lo.n_blocks; ++k)
+      if (i >= P.lo.off[k]) b = k;
+    const float v = P.qmul[b] > 0 ? dpool[P.poff[b] + i - P.lo.off[b]] : 0.f;
+    for (int n = nb; n < ne; ++n) d_o[(int64_t)n * P.lo.stride + i] = v;
+  }
+}
+
+// dWq_b[u][w] = scale_b sum_g sum_m pooled[g][b][m][u] dq[g][b][w][m];  dbias[w] = sum_g dq[g][0][w][0]
+__global__ void k_tail_wgrad(const float* __restrict__ pooled, const float* __restrict__ dq, float* __restrict__ dWq,
+                             float* __restrict__ dbias, int64_t G, TailBwdParams P, int n_w) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_w) {
+    int b = -1;
+    for (int k = 0; k < P.lo.n_blocks; ++k)
+      if (P.qmul[k] > 0 && i >= P.woff[k]) b = k;
+    const int rows = P.lo.rows[b], mul = P.lo.mul[b], r = i - P.woff[b];
+    const int u = r / P.qmul[b], w = r % P.qmul[b];
+    float s = 0.f;
+    for (int64_t g = 0; g < G; ++g)
+      for (int m = 0; m < rows; ++m) s = fmaf(pooled[g * P.npool + P.poff[b] + m * mul + u], dq[g * P.nq + P.qoff[b] + w * rows + m], s);
+    dWq[i] = s * P.qscale[b];
+  } else if (dbias != nullptr && i < n_w + P.qmul[0]) {
+    const int w = i - n_w;
+    float s = 0.f;
+    for (int64_t g = 0; g < G; ++g) s += dq[g * P.nq + P.qoff[0] + w * P.lo.rows[0]];
+    dbias[w] = s;
+  }
+}
+
+void fill_tail(TailBwdParams& T, const EegLayout* lo, const int32_t* host_qmul, const float* host_qscale, int positive, int reduce,
+               int* n_w) {
+  T.lo = *lo;
+  int nq = 0, npool = 0, woff = 0;
+  for (int b = 0; b < EEG_MAX_L; ++b) { T.qmul[b] = 0; T.qoff[b] = 0; T.woff[b] = 0; T.poff[b] = 0; T.qscale[b] = 0.f; }
+  for (int b = 0; b < lo->n_blocks; ++b) {
+    T.qmul[b] = host_qmul[b];
+    T.qscale[b] = host_qscale[b];
+    T.qoff[b] = nq;
+    T.woff[b] = woff;
+    T.poff[b] = npool;
+    if (host_qmul[b] > 0) {
+      nq += host_qmul[b] * lo->rows[b];
+      woff += host_qmul[b] * lo->mul[b];
+      npool += lo->rows[b] * lo->mul[b];
+    }
+  }
+  T.nq = nq; T.npool = npool; T.positive = positive; T.reduce = reduce;
+  *n_w = woff;
+}
+
+}  // namespace
+
+extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
+                                      const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
+                                      const int32_t* k_override, float* dW, float* dbias, int64_t N, void* stream) {
+  EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_wgrad: layout mismatch");
+  if (N == 0) return 0;
+  WgParams P;
+  P.n_blocks = lin->n_blocks;
+  P.in_stride = lin->stride;
+  P.out_stride = lout->stride;
+  P.transB = transB;
+  int64_t ctas = 0;
+  for (int b = 0; b < P.n_blocks; ++b) {
+    EEG_REQUIRE(lin->rows[b] == lout->rows[b], "eeg_block_linear_wgrad: block %d rows differ", b);
+    WgBlock& d = P.b[b];
+    d.rows = lin->rows[b];
+    d.k = k_override ? k_override[b] : lin->mul[b];
+    d.in_ld = in_ld ? in_ld[b] : lin->mul[b];
+    d.nout = lout->mul[b];
+    d.in_off = lin->off[b];
+    d.out_off = lout->off[b];
+    d.w_off = host_w_off[b];
+    d.scale = host_scale[b];
+    EEG_REQUIRE(d.k % 4 == 0 && d.nout % 4 == 0 && d.in_off % 4 == 0 && d.out_off % 4 == 0 && d.in_ld % 4 == 0 &&
+                    lin->stride % 4 == 0 && lout->stride % 4 == 0,
+                "eeg_block_linear_wgrad: block %d not float4-aligned", b);
+    d.cta_begin = (int)ctas;
+    d.ktiles = (d.k + 31) / 32;
+    d.ntiles = (d.nout + 31) / 32;
+    const int64_t chunks = (N * d.rows + WG_ROWS - 1) / WG_ROWS;
+    ctas += (d.k > 0 && d.nout > 0) ? chunks * d.ktiles * d.ntiles : 0;
+    if (d.k == 0 || d.nout == 0) { d.ktiles = 1; d.ntiles = 1; }
+    EEG_REQUIRE(ctas < (1LL << 31), "eeg_block_linear_wgrad: too many tiles");
+  }
+  if (ctas == 0) return 0;
+  k_linear_wgrad<<<(unsigned)ctas, 128, 0, (cudaStream_t)stream>>>(x, dy, dW, dbias, N, P);
+  EEG_CHECK_LAUNCH("eeg_block_linear_wgrad");
+  return 0;
+}
+
+extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream) {
+  if (R == 0 || cols == 0) return 0;
+  const int rows_per_cta = 1024;
+  dim3 grid((unsigned)((R + rows_per_cta - 1) / rows_per_cta), (unsigned)((cols + 127) / 128));
+  k_colsum<<<grid, 128, 0, (cudaStream_t)stream>>>(x, R, ld, cols, row_scale, out, rows_per_cta);
+  EEG_CHECK_LAUNCH("eeg_colsum");
+  return 0;
+}
+
+extern "C" int eeg_silu_fwd(const float* a, float* s, int64_t n, void* stream) {
+  if (n == 0) return 0;
+  k_silu_fwd<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(a, s, n);
+  EEG_CHECK_LAUNCH("eeg_silu_fwd");
+  return 0;
+}
+extern "C" int eeg_silu_bwd(const float* a, const float* ds, float* da, int64_t n, void* stream) {
+  if (n == 0) return 0;
+  k_silu_bwd<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(a, ds, da, n);
+  EEG_CHECK_LAUNCH("eeg_silu_bwd");
+  return 0;
+}
+
+extern "C" int eeg_gate_bwd(const float* z, const EegLayout* lz, const float* dg, const EegLayout* lg, int n_scalars, float act_const,
+                            float* dz, int64_t N, void* stream) {
+  EEG_REQUIRE(lz && lg && lz->n_blocks == lg->n_blocks, "eeg_gate_bwd: layout mismatch");
+  if (N == 0) return 0;
+  GateBwdParams P;
+  P.lz = *lz;
+  P.lg = *lg;
+  P.n_scalars = n_scalars;
+  P.c = act_const;
+  int go = n_scalars;
+  for (int b = 0; b < EEG_MAX_L; ++b) P.gate_off[b] = 0;
+  for (int b = 1; b < lz->n_blocks; ++b) {
+    P.gate_off[b] = lz->off[0] + go;
+    go += lz->mul[b];
+  }
+  k_gate_bwd<<<(unsigned)N, 128, 0, (cudaStream_t)stream>>>(z, dg, dz, P);
+  EEG_CHECK_LAUNCH("eeg_gate_bwd");
+  return 0;
+}
+
+extern "C" int eeg_pool_tail_bwd(const float* o, const EegLayout* lo, const int32_t* graph_ptr, const float* Wq,
+                                 const int32_t* host_qmul, const float* host_qscale, const float* P, int positive, int reduce,
+                                 const float* A, const float* dC, float* d_o, float* dq_ws /*[G,nq]*/, float* pooled_ws /*[G,npool]*/,
+                                 float* dWq, float* dbias, int64_t G, void* stream) {
+  EEG_REQUIRE(lo && lo->n_blocks <= EEG_MAX_L && positive >= 0 && positive <= 4, "eeg_pool_tail_bwd: bad arguments");
+  if (G == 0) return 0;
+  TailBwdParams T;
+  int n_w = 0;
+  fill_tail(T, lo, host_qmul, host_qscale, positive, reduce, &n_w);
+  const size_t smem = (size_t)(T.npool + T.nq + 36 * 5) * sizeof(float);
+  EEG_REQUIRE(smem <= 48 * 1024, "eeg_pool_tail_bwd: pooled row too large");
+  k_pool_tail_bwd<<<(unsigned)G, 128, smem, (cudaStream_t)stream>>>(o, graph_ptr, Wq, P, A, dC, d_o, dq_ws, pooled_ws, T);
+  EEG_CHECK_LAUNCH("eeg_pool_tail_bwd");
+  const int tot = n_w + (dbias ? T.qmul[0] : 0);
+  k_tail_wgrad<<<(tot + 127) / 128, 128, 0, (cudaStream_t)stream>>>(pooled_ws, dq_ws, dWq, dbias, G, T, n_w);
+  EEG_CHECK_LAUNCH("eeg_tail_wgrad");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ optimizer
+// torch.optim.AdamW(amsgrad) + Lightning gradient_clip_val (scripts/train_utils.py:38-44, scripts/train_main.py:89-92) on
+// one flat fp32 buffer: g <- grad_scale * g (e.g. 1/world after an all-reduce sum), clipped by max_norm / (|g| + 1e-6).
+namespace {
+__global__ void k_sumsq(const float* __restrict__ x, int64_t n, float* __restrict__ out) {
+  float s = 0.f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) s = fmaf(x[i], x[i], s);
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ float ws[8];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += ws[w];
+    atomicAdd(out, t);
+  }
+}
+__global__ void k_adamw(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                        float* __restrict__ vmax, int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2,
+                        const float* __restrict__ gnorm_sq, float max_norm, float grad_scale) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float clip = grad_scale;
+  if (gnorm_sq != nullptr && max_norm > 0.f) {
+    const float nrm = sqrtf(gnorm_sq[0]) * grad_scale;
+    clip *= fminf(max_norm / (nrm + 1e-6f), 1.0f);
+  }
+  const float gi = g[i] * clip;
+  float pi = p[i] * (1.0f - lr * wd);                    // decoupled weight decay
+  const float mi = b1 * m[i] + (1.0f - b1) * gi;
+  const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+  m[i] = mi;
+  v[i] = vi;
+  float vh = vi;
+  if (vmax != nullptr) {
+    vh = fmaxf(vmax[i], vi);
+    vmax[i] = vh;
+  }
+  p[i] = pi - (lr / bc1) * mi / (sqrtf(vh) / sqrtf(bc2) + eps);
+}
+}  // namespace
+
+extern "C" int eeg_sumsq(const float* x, int64_t n, float* out, void* stream) {
+  if (n == 0) return 0;
+  const unsigned grid = (unsigned)((n + 255) / 256 < 1024 ? (n + 255) / 256 : 1024);
+  k_sumsq<<<grid, 256, 0, (cudaStream_t)stream>>>(x, n, out);
+  EEG_CHECK_LAUNCH("eeg_sumsq");
+  return 0;
+}
+
+extern "C" int eeg_adamw_step(float* p, const float* g, float* m, float* v, float* vmax, int64_t n, float lr, float beta1, float beta2,
+                              float eps, float weight_decay, int step, const float* gnorm_sq, float max_norm, float grad_scale,
+                              void* stream) {
+  EEG_REQUIRE(step >= 1, "eeg_adamw_step: step counts from 1");
+  if (n == 0) return 0;
+  const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
+  k_adamw<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, vmax, n, lr, beta1, beta2, eps, weight_decay, bc1, bc2,
+                                                                        gnorm_sq, max_norm, grad_scale);
+  EEG_CHECK_LAUNCH("eeg_adamw_step");
+  return 0;
+}

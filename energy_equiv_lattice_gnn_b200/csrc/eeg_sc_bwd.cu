@@ -1,0 +1,229 @@
+// Symmetric contraction (gnn/mace.py:112-277), backward.  The reference differentiates its einsum chain with autograd;
+// here the two gradients are explicit:
+//   eeg_sym_contract_bwd_x : dx[n,d,c] = sum_M dout[n,M,c] dP_M/dx_d, reverse-mode sweep of the same Horner tree and
+//                            coefficient stream as the forward (generated macro program, packed FFMA2 on node pairs)
+//   eeg_sc_coef_grad       : dT[z][c,slot] = sum_{n in node slice z} dout[n,M(slot),c] * monomial_slot(x[n,:,c])  (table
+//                            driven; a warp owns a few slots, lane = channel, fixed node order; EEG_SC_GRAD_SLICES
+//                            partial sums, no atomics: deterministic)
+//   eeg_sc_coefficients_bwd: dW[k,c] = sum_slot A[slot,k] sum_z dT[z][c,slot]   (transpose of eeg_sc_coefficients)
+#include "eeg_common.cuh"
+#include "generated/scb_l3_nu3.cuh"
+#include "generated/scb_l4_nu3.cuh"
+
+namespace {
+
+constexpr int CH = 2, TPC = 128, THREADS = CH * TPC, NT = 2 * TPC;   // 2 channels x 256 nodes per tile, node pairs per thread
+
+typedef unsigned long long p2;  // two fp32 lanes (node A, node B)
+__device__ __forceinline__ p2 pk(float a, float b) { p2 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(a), "f"(b)); return d; }
+__device__ __forceinline__ p2 ffma2(p2 a, p2 b, p2 c) { p2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ p2 fmul2(p2 a, p2 b) { p2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ void unpk(p2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+
+#define Q(n) const float4 q##n = T4[n];
+#define GM(M) g = pk(dsin[(M) * NT], dsin[(M) * NT + TPC]);
+#define GI(i) gi = fmul2(g, x[i]);
+#define S1(c) m1 = pk((c), (c));
+#define Z1() m1 = 0ull;
+#define GJ(j) gij = fmul2(gi, x[j]);
+#define S2(c) m2 = pk((c), (c));
+#define Z2() m2 = 0ull;
+#define B3(c, t) m2 = ffma2(pk((c), (c)), x[t], m2); dx[t] = ffma2(pk((c), (c)), gij, dx[t]);
+#define E2(j) m1 = ffma2(m2, x[j], m1); dx[j] = ffma2(gi, m2, dx[j]);
+#define E1(i) dx[i] = ffma2(g, m1, dx[i]);
+
+template <int LMAX>
+struct ProgB;
+template <>
+struct ProgB<4> {
+  static constexpr int NCOEF = EEG_SCB_l4_nu3_NCOEF, D = 25;
+  static __device__ __forceinline__ void run(const p2* __restrict__ x, p2* __restrict__ dx, const float4* __restrict__ T4,
+                                             const float* __restrict__ dsin) {
+    p2 g, gi, gij, m1, m2;
+    EEG_SCB_l4_nu3_PROGRAM
+  }
+};
+template <>
+struct ProgB<3> {
+  static constexpr int NCOEF = EEG_SCB_l3_nu3_NCOEF, D = 16;
+  static __device__ __forceinline__ void run(const p2* __restrict__ x, p2* __restrict__ dx, const float4* __restrict__ T4,
+                                             const float* __restrict__ dsin) {
+    p2 g, gi, gij, m1, m2;
+    EEG_SCB_l3_nu3_PROGRAM
+  }
+};
+
+template <int LMAX>
+__global__ void __launch_bounds__(THREADS, 1) k_sc_bwd_x(const float* __restrict__ xg, const float* __restrict__ dog,
+                                                         const float* __restrict__ T, float* __restrict__ dxg, int64_t N, int C,
+                                                         int tiles_per_cta) {
+  using F = ProgB<LMAX>;
+  constexpr int D = F::D, NCOEF = F::NCOEF;
+  extern __shared__ __align__(16) float smem[];
+  float* Ts = smem;                     // [CH][NCOEF]
+  float* xs = Ts + CH * NCOEF;          // [CH][D][NT]   x tile, then the dx tile
+  float* ds = xs + CH * D * NT;         // [CH][D][NT]   dout tile
+  const int t = threadIdx.x;
+  const int c0 = blockIdx.x * CH;
+  {
+    const float4* src = reinterpret_cast<const float4*>(T + (int64_t)c0 * NCOEF);
+    float4* dst = reinterpret_cast<float4*>(Ts);
+    for (int i = t; i < CH * NCOEF / 4; i += THREADS) dst[i] = __ldg(src + i);
+  }
+  const int nl = t % TPC, cc = t / TPC;
+  const int64_t n_tiles = (N + NT - 1) / NT;
+  const int64_t tile_begin = (int64_t)blockIdx.y * tiles_per_cta;
+  for (int64_t tile = tile_begin; tile < tile_begin + tiles_per_cta && tile < n_tiles; ++tile) {
+    const int64_t n0 = tile * NT;
+    __syncthreads();
+    for (int idx = t; idx < NT * D; idx += THREADS) {
+      const int n_l = idx % NT, d = idx / NT;
+      float2 v = make_float2(0.f, 0.f), w = make_float2(0.f, 0.f);
+      if (n0 + n_l < N) {
+        v = __ldg(reinterpret_cast<const float2*>(xg + ((n0 + n_l) * D + d) * (int64_t)C + c0));
+        w = __ldg(reinterpret_cast<const float2*>(dog + ((n0 + n_l) * D + d) * (int64_t)C + c0));
+      }
+      xs[(0 * D + d) * NT + n_l] = v.x;
+      xs[(1 * D + d) * NT + n_l] = v.y;
+      ds[(0 * D + d) * NT + n_l] = w.x;
+      ds[(1 * D + d) * NT + n_l] = w.y;
+    }
+    __syncthreads();
+    p2 xv[D], dxv[D];
+    float* xin = xs + cc * D * NT + nl;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      xv[d] = pk(xin[d * NT], xin[d * NT + TPC]);
+      dxv[d] = 0ull;
+    }
+    F::run(xv, dxv, reinterpret_cast<const float4*>(Ts + cc * NCOEF), ds + cc * D * NT + nl);
+#pragma unroll
+    for (int d = 0; d < D; ++d) {  // this thread's own x slots become its dx
+      float a, b;
+      unpk(dxv[d], a, b);
+      xin[d * NT] = a;
+      xin[d * NT + TPC] = b;
+    }
+    __syncthreads();
+    for (int idx = t; idx < NT * D; idx += THREADS) {
+      const int n_l = idx % NT, d = idx / NT;
+      if (n0 + n_l < N)
+        *reinterpret_cast<float2*>(dxg + ((n0 + n_l) * D + d) * (int64_t)C + c0) =
+            make_float2(xs[(0 * D + d) * NT + n_l], xs[(1 * D + d) * NT + n_l]);
+    }
+  }
+}
+
+template <int LMAX>
+int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float* dx, int64_t N, cudaStream_t s) {
+  using F = ProgB<LMAX>;
+  const size_t smem = (size_t)(CH * F::NCOEF + 2 * CH * F::D * NT) * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k_sc_bwd_x<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+      eeg_set_error("eeg_sym_contract_bwd_x: cannot opt in to %zu B shared memory: %s", smem, cudaGetErrorString(e));
+      return 2;
+    }
+    attr_set = true;
+  }
+  const int groups = C / CH;
+  const int64_t n_tiles = (N + NT - 1) / NT;
+  int slices = EEG_NUM_SMS / groups;
+  if (slices > n_tiles) slices = (int)n_tiles;
+  if (slices < 1) slices = 1;
+  const int tiles_per_cta = (int)((n_tiles + slices - 1) / slices);
+  slices = (int)((n_tiles + tiles_per_cta - 1) / tiles_per_cta);
+  k_sc_bwd_x<LMAX><<<dim3(groups, slices), THREADS, smem, s>>>(x, dout, T, dx, N, C, tiles_per_cta);
+  EEG_CHECK_LAUNCH("eeg_sym_contract_bwd_x");
+  return 0;
+}
+
+// ---- dT: a warp owns slots {w0, w0 + stride, ...} (at most SLOTS_PER_WARP), lane = channel chunk element --------------
+constexpr int CG_WARPS = 8, CG_SPW = 8;   // warps per CTA, slots per warp
+
+__global__ void __launch_bounds__(CG_WARPS * 32) k_sc_coef_grad(const float* __restrict__ x, const float* __restrict__ dout,
+                                                                 const int4* __restrict__ slot_tab, int n_coef, int D, int C,
+                                                                 int64_t N, float* __restrict__ dT) {
+  const int64_t per = (N + gridDim.z - 1) / gridDim.z;
+  const int64_t n_begin = blockIdx.z * per, n_end = n_begin + per < N ? n_begin + per : N;
+  dT += (int64_t)blockIdx.z * C * n_coef;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int chunk = blockIdx.y;                       // 32-channel chunk
+  const int s0 = (blockIdx.x * CG_WARPS + warp) * CG_SPW;
+  if (s0 >= n_coef) return;
+  int4 tab[CG_SPW];
+  float acc[CG_SPW];
+#pragma unroll
+  for (int q = 0; q < CG_SPW; ++q) {
+    tab[q] = s0 + q < n_coef ? __ldg(slot_tab + s0 + q) : make_int4(-1, -1, -1, -1);
+    acc[q] = 0.f;
+  }
+  const int c = chunk * 32 + lane;
+  const float* xb = x + c;
+  const float* db = dout + c;
+  for (int64_t n = n_begin; n < n_end; ++n) {
+    const int64_t base = n * D * (int64_t)C;
+#pragma unroll
+    for (int q = 0; q < CG_SPW; ++q) {
+      const int4 e = tab[q];   // (M, i, j, t); -1 = absent
+      if (e.x < 0) continue;   // warp-uniform
+      float v = __ldg(db + base + (int64_t)e.x * C) * __ldg(xb + base + (int64_t)e.y * C);
+      if (e.z >= 0) v *= __ldg(xb + base + (int64_t)e.z * C);
+      if (e.w >= 0) v *= __ldg(xb + base + (int64_t)e.w * C);
+      acc[q] += v;
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < CG_SPW; ++q)
+    if (s0 + q < n_coef) dT[(int64_t)c * n_coef + s0 + q] = acc[q];
+}
+
+__global__ void k_sc_coefficients_bwd(const int32_t* __restrict__ tp, const int32_t* __restrict__ trow, const float* __restrict__ tval,
+                                      int n_wrows, int n_coef, const float* __restrict__ dT, int n_slices, int C,
+                                      float* __restrict__ dW) {
+  const int k = blockIdx.x * blockDim.y + threadIdx.y;
+  if (k >= n_wrows) return;
+  for (int c = threadIdx.x; c < C; c += 32) {
+    float s = 0.f;
+    for (int q = tp[k]; q < tp[k + 1]; ++q) {
+      const int64_t o = (int64_t)c * n_coef + __ldg(trow + q);
+      float d = 0.f;
+      for (int z = 0; z < n_slices; ++z) d += __ldg(dT + (int64_t)z * C * n_coef + o);
+      s = fmaf(__ldg(tval + q), d, s);
+    }
+    dW[(int64_t)k * C + c] = s;
+  }
+}
+
+}  // namespace
+
+extern "C" int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, const float* dout, const float* T, float* dx,
+                                      int64_t N, void* stream) {
+  EEG_REQUIRE(nu == 3 && (lmax == 3 || lmax == 4), "eeg_sym_contract_bwd_x: unsupported (lmax=%d, correlation=%d)", lmax, nu);
+  EEG_REQUIRE(C > 0 && C % CH == 0, "eeg_sym_contract_bwd_x: C must be a multiple of %d", CH);
+  if (N == 0) return 0;
+  return lmax == 4 ? launch_bwd_x<4>(C, x, dout, T, dx, N, (cudaStream_t)stream) : launch_bwd_x<3>(C, x, dout, T, dx, N, (cudaStream_t)stream);
+}
+
+extern "C" int eeg_sc_grad_slices(void) { return 16; }
+
+extern "C" int eeg_sc_coef_grad(const float* x, const float* dout, const int32_t* slot_tab, int n_coef, int D, int C, int64_t N,
+                                float* dT, void* stream) {
+  EEG_REQUIRE(C > 0 && C % 32 == 0, "eeg_sc_coef_grad: C must be a multiple of 32");
+  if (n_coef == 0) return 0;
+  dim3 grid(eeg_div_up(n_coef, CG_WARPS * CG_SPW), C / 32, eeg_sc_grad_slices());   // N == 0: slices are written as zeros
+  k_sc_coef_grad<<<grid, CG_WARPS * 32, 0, (cudaStream_t)stream>>>(x, dout, reinterpret_cast<const int4*>(slot_tab), n_coef, D, C, N, dT);
+  EEG_CHECK_LAUNCH("eeg_sc_coef_grad");
+  return 0;
+}
+
+extern "C" int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,
+                                       const float* dT, int C, float* dW, void* stream) {
+  const int n_slices = eeg_sc_grad_slices();
+  if (n_wrows == 0) return 0;
+  dim3 block(32, 8), grid(eeg_div_up(n_wrows, 8));
+  k_sc_coefficients_bwd<<<grid, block, 0, (cudaStream_t)stream>>>(t_ptr, t_row, t_val, n_wrows, n_coef, dT, n_slices, C, dW);
+  EEG_CHECK_LAUNCH("eeg_sc_coefficients_bwd");
+  return 0;
+}

@@ -1,0 +1,126 @@
+// Backward of the channelwise tensor-product message + scatter (gnn/blocks.py:591-597).
+//   dw[e, p*C + c]      = inv_norm * sum_k dM[recv(e), row(p,k), c] * t_{p,k}(h'[send(e)], Y_e)          (edge-major, CSR order)
+//   dh'[send(e), i, c] += inv_norm * sum_p w[e,p,c] sum_k G_p[i,k](Y_e) dM[recv(e), row(p,k), c]          (atomic adds)
+// One warp per run of 16 receiver rows (contiguous CSR edges), lane = channel; per edge the lane-uniform matrices
+// G_p[i,k] = sum_j C_p[i,j,k] Y_j are staged once per warp in shared memory (the forward's table), then a generated
+// straight-line function (tools/gen_kernels.py: gen_tp2_bwd) evaluates every path.
+#include "eeg_common.cuh"
+#include "generated/tp2_0_3.cuh"
+#include "generated/tp2_0_4.cuh"
+#include "generated/tp2_3_3.cuh"
+#include "generated/tp2_4_4.cuh"
+#include "generated/tp2b_0_3.cuh"
+#include "generated/tp2b_0_4.cuh"
+#include "generated/tp2b_3_3.cuh"
+#include "generated/tp2b_4_4.cuh"
+
+namespace {
+
+constexpr int WARPS = 4, NPW = 16;
+
+template <int LIN, int LMAX>
+struct TpB;
+#define EEG_TPB(LIN, LMAX)                                                                                          \
+  template <>                                                                                                       \
+  struct TpB<LIN, LMAX> {                                                                                           \
+    static constexpr int NTAB = EEG_TP2_##LIN##_##LMAX##_NTAB, ROWS = EEG_TP2_##LIN##_##LMAX##_ROWS,                 \
+                         NPATHS = EEG_TP2_##LIN##_##LMAX##_NPATHS;                                                  \
+    static __device__ __forceinline__ const int4* tab() { return eeg_tp2_##LIN##_##LMAX##_tab; }                    \
+    static __device__ __forceinline__ void run(const float* x, const float4* G4, const float* wp, long ws, const float* dMp, \
+                                               long cs, float* dwp, float* dx) {                                    \
+      eeg_tp2b_##LIN##_##LMAX(x, G4, wp, ws, dMp, cs, dwp, dx);                                                     \
+    }                                                                                                               \
+  };
+EEG_TPB(0, 3) EEG_TPB(0, 4) EEG_TPB(3, 3) EEG_TPB(4, 4)
+#undef EEG_TPB
+
+template <int LIN, int LMAX>
+__global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
+                                                       const float* __restrict__ w_t, int64_t E, const int32_t* __restrict__ sender,
+                                                       const int32_t* __restrict__ row_ptr, float inv_norm, const float* __restrict__ dM,
+                                                       float* __restrict__ dw, float* __restrict__ dh, int64_t N, int C, int chunks) {
+  using I = TpB<LIN, LMAX>;
+  constexpr int DIN = (LIN + 1) * (LIN + 1);
+  extern __shared__ __align__(16) uint8_t tpb_smem[];
+  int4* tab_s = reinterpret_cast<int4*>(tpb_smem);
+  for (int i = threadIdx.x; i < I::NTAB; i += WARPS * 32) tab_s[i] = I::tab()[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* Gs = reinterpret_cast<float*>(tpb_smem + (size_t)I::NTAB * 16) + (size_t)wid * I::NTAB;
+  const int chunk = blockIdx.x % chunks;
+  const int64_t n0 = ((int64_t)(blockIdx.x / chunks) * WARPS + wid) * NPW;
+  if (n0 >= N) return;
+  const int64_t n1 = n0 + NPW < N ? n0 + NPW : N;
+  const int c = chunk * 32 + lane;
+  const int64_t wstride = (int64_t)chunks * E * 32;   // floats between consecutive paths of w_t
+  int ee = __ldg(row_ptr + n0);
+  for (int64_t n = n0; n < n1; ++n) {
+    const int eb = ee;
+    ee = __ldg(row_ptr + n + 1);
+    const float* dMp = dM + n * (int64_t)I::ROWS * C + c;
+    for (int e = eb; e < ee; ++e) {
+      const int s = __ldg(sender + e);
+      const float yv = lane < ystride ? __ldg(Y + (int64_t)e * ystride + lane) : 0.f;
+      __syncwarp();
+      for (int q = lane; q < I::NTAB; q += 32) {
+        const int4 t = tab_s[q];
+        const float y0 = __shfl_sync(0xffffffffu, yv, t.x);
+        const float y1 = __shfl_sync(0xffffffffu, yv, t.z);
+        Gs[q] = fmaf(__int_as_float(t.y), y0, __int_as_float(t.w) * y1);
+      }
+      float x[DIN], dx[DIN];
+#pragma unroll
+      for (int d = 0; d < DIN; ++d) {
+        x[d] = __ldg(h + ((int64_t)s * DIN + d) * C + c);
+        dx[d] = 0.f;
+      }
+      __syncwarp();
+      float* dwp = dw + (int64_t)e * I::NPATHS * C + c;
+      I::run(x, reinterpret_cast<const float4*>(Gs), w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane, wstride, dMp, C, dwp, dx);
+      // fold 1 / agg_norm_const
+#pragma unroll
+      for (int p = 0; p < I::NPATHS; ++p) dwp[(int64_t)p * C] *= inv_norm;
+#pragma unroll
+      for (int d = 0; d < DIN; ++d) atomicAdd(dh + ((int64_t)s * DIN + d) * C + c, dx[d] * inv_norm);
+    }
+  }
+}
+
+template <int LIN, int LMAX>
+int launch_tpb(const float* h, const float* Y, int ystride, const float* w_t, int64_t E, const int32_t* sender, const int32_t* row_ptr,
+               float inv_norm, const float* dM, float* dw, float* dh, int64_t N, int C, cudaStream_t s) {
+  using I = TpB<LIN, LMAX>;
+  const size_t smem = (size_t)I::NTAB * 16 + (size_t)WARPS * I::NTAB * 4;
+  static bool attr_set = false;
+  if (!attr_set && smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(k_tp_bwd<LIN, LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) {
+      eeg_set_error("eeg_tp_scatter_bwd: cannot opt in to %zu B shared memory: %s", smem, cudaGetErrorString(e));
+      return 2;
+    }
+    attr_set = true;
+  }
+  const int chunks = C / 32;
+  k_tp_bwd<LIN, LMAX><<<(unsigned)(eeg_div_up(N, WARPS * NPW) * chunks), WARPS * 32, smem, s>>>(h, Y, ystride, w_t, E, sender, row_ptr,
+                                                                                                inv_norm, dM, dw, dh, N, C, chunks);
+  EEG_CHECK_LAUNCH("eeg_tp_scatter_bwd");
+  return 0;
+}
+
+}  // namespace
+
+// dw [E, n_paths*C] (CSR order) is fully written; dh [N, (lmax_in+1)^2, C] must be zero-initialised by the caller.
+extern "C" int eeg_tp_scatter_bwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
+                                  int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, const float* dM,
+                                  float* dw, float* dh, int64_t N, void* stream) {
+  EEG_REQUIRE(C > 0 && C % 32 == 0, "eeg_tp_scatter_bwd: C must be a multiple of 32 (got %d)", C);
+  if (N == 0 || E == 0) return 0;
+  EEG_REQUIRE(ystride % 4 == 0 && ystride <= 32, "eeg_tp_scatter_bwd: ystride must be a multiple of 4 and <= 32 (got %d)", ystride);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (lmax_in == 0 && lmax == 3) return launch_tpb<0, 3>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
+  if (lmax_in == 3 && lmax == 3) return launch_tpb<3, 3>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
+  if (lmax_in == 0 && lmax == 4) return launch_tpb<0, 4>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
+  if (lmax_in == 4 && lmax == 4) return launch_tpb<4, 4>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
+  eeg_set_error("eeg_tp_scatter_bwd: unsupported (lmax_in=%d, lmax=%d)", lmax_in, lmax);
+  return 1;
+}

@@ -172,6 +172,12 @@ class EnergyEquivGNN(torch.nn.Module):
         self._cache[("radial", i)] = (key, img, bh)
         return img, bh
 
+    def _cache_bump(self):
+        """Drop weight-derived tables (SC coefficients, radial operand image) after an in-place optimizer step that
+        bypasses torch's version counters (train.FlatAdamW updates the flat parameter buffer through the C ABI)."""
+        for k in [k for k in self._cache if isinstance(k, tuple)]:
+            del self._cache[k]
+
     def _tail_matrix(self) -> torch.Tensor:
         """P[nq, 36]: q -> Mandel matrix A (Spherical_to_Cartesian then Cart_4_to_Mandel, gnn/blocks.py:392-442)."""
         head = self.stiffness_head

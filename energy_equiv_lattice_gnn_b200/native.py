@@ -19,6 +19,10 @@ SYMBOLS = [
     "eeg_last_error", "eeg_abi_version", "eeg_csr_workspace_bytes", "eeg_csr_build", "eeg_graph_ptr",
     "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_gate_linear_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
     "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd", "eeg_radial_image_floats", "eeg_radial_pack", "eeg_radial_mlp_fwd",
+    # explicit backward ops + optimizer
+    "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
+    "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
+    "eeg_sumsq", "eeg_adamw_step",
 ]
 
 
@@ -64,7 +68,7 @@ def lib() -> C.CDLL:
 KERNELS_PER_CALL = {"eeg_csr_build": 6, "eeg_graph_ptr": 1, "eeg_node_embed_fwd": 1, "eeg_edge_featurize": 1,
                     "eeg_block_linear_fwd": 1, "eeg_gate_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
                     "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1,
-                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1}
+                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1, "eeg_pool_tail_bwd": 2}
 launch_count = 0
 _events = None  # list of (name, tag, start_event, end_event) while profiling
 _tag = ""
@@ -275,3 +279,119 @@ def pool_tail(o, lo: EegLayout, gp, Wq, qmul: Sequence[int], qscale: Sequence[fl
                                    C.c_int(positive), C.c_int(reduce), _p(q_out), _p(A_out), _p(Cout), C.c_int64(num_graphs),
                                    _stream()), "eeg_pool_tail_fwd")
     return Cout, q_out, A_out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# explicit backward ops (include/eeg_b200.h, "backward" section)
+def _arr(ctype, vals, n=EEG_MAX_L, fill=0):
+    vals = list(vals)
+    return (ctype * n)(*(vals + [fill] * (n - len(vals))))
+
+
+def linear_wgrad(x, lin: EegLayout, dy, lout: EegLayout, w_off, scale, n_weights: int, n_rows: int, transB=False, want_bias=0):
+    """-> (dW [n_weights], dbias [want_bias] or None); dW_b[u,w] = scale_b sum_rows x[.,u] dy[.,w]."""
+    dW = torch.zeros(n_weights, dtype=f32, device=x.device)
+    db = torch.zeros(want_bias, dtype=f32, device=x.device) if want_bias else None
+    _begin("eeg_block_linear_wgrad")
+    _check(lib().eeg_block_linear_wgrad(_p(x, f32), C.byref(lin), _p(dy, f32), C.byref(lout), _arr(C.c_int64, w_off), _arr(C.c_float, scale, fill=0.0),
+                                        C.c_int(int(transB)), C.c_void_p(0), C.c_void_p(0), _p(dW), _p(db), C.c_int64(n_rows), _stream()),
+           "eeg_block_linear_wgrad")
+    return dW, db
+
+
+def colsum(x, row_scale=None):
+    """out[c] = sum_r row_scale[r] * x[r, c] for a 2-D contiguous x."""
+    R, cols = x.shape
+    out = torch.zeros(cols, dtype=f32, device=x.device)
+    _begin("eeg_colsum")
+    _check(lib().eeg_colsum(_p(x, f32), C.c_int64(R), C.c_int(cols), C.c_int(cols), _p(row_scale, f32), _p(out), _stream()), "eeg_colsum")
+    return out
+
+
+def silu_fwd(a):
+    s = torch.empty_like(a)
+    _begin("eeg_silu_fwd")
+    _check(lib().eeg_silu_fwd(_p(a, f32), _p(s), C.c_int64(a.numel()), _stream()), "eeg_silu_fwd")
+    return s
+
+
+def silu_bwd(a, ds):
+    da = torch.empty_like(a)
+    _begin("eeg_silu_bwd")
+    _check(lib().eeg_silu_bwd(_p(a, f32), _p(ds, f32), _p(da), C.c_int64(a.numel()), _stream()), "eeg_silu_bwd")
+    return da
+
+
+def gate_bwd(z, lz: EegLayout, dg, lg: EegLayout, n_scalars: int, act_const: float, n_nodes: int):
+    dz = torch.empty_like(z)
+    _begin("eeg_gate_bwd")
+    _check(lib().eeg_gate_bwd(_p(z, f32), C.byref(lz), _p(dg, f32), C.byref(lg), C.c_int(n_scalars), C.c_float(act_const), _p(dz),
+                              C.c_int64(n_nodes), _stream()), "eeg_gate_bwd")
+    return dz
+
+
+def pool_tail_bwd(o, lo: EegLayout, gp, Wq, qmul, qscale, bias_len: int, P, positive: int, reduce: int, A, dC, num_graphs: int):
+    """-> (d_o [N, lo.stride], dWq, dbias)"""
+    dev = o.device
+    nb = lo.n_blocks
+    nq = sum(q * lo.rows[b] for b, q in enumerate(qmul))
+    npool = sum(lo.rows[b] * lo.mul[b] for b, q in enumerate(qmul) if q > 0)
+    d_o = torch.empty_like(o)
+    dq = torch.empty(num_graphs, nq, dtype=f32, device=dev)
+    pooled = torch.empty(num_graphs, npool, dtype=f32, device=dev)
+    dWq = torch.empty_like(Wq)
+    db = torch.empty(bias_len, dtype=f32, device=dev) if bias_len else None
+    _begin("eeg_pool_tail_bwd")
+    _check(lib().eeg_pool_tail_bwd(_p(o, f32), C.byref(lo), _p(gp, i32), _p(Wq, f32), _arr(C.c_int32, qmul), _arr(C.c_float, qscale, fill=0.0),
+                                   _p(P, f32), C.c_int(positive), C.c_int(reduce), _p(A, f32), _p(dC, f32), _p(d_o), _p(dq), _p(pooled),
+                                   _p(dWq), _p(db), C.c_int64(num_graphs), _stream()), "eeg_pool_tail_bwd")
+    return d_o, dWq, db
+
+
+def tp_scatter_bwd(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, dM, n_paths, n_nodes):
+    """-> (dw [E, n_paths*C] edge-major CSR order, dh [N, (lmax_in+1)^2 * C])"""
+    E = w_t.shape[1]
+    dw = torch.empty(E, n_paths * Cch, dtype=f32, device=h.device)
+    dh = torch.zeros_like(h)
+    _begin("eeg_tp_scatter_bwd")
+    _check(lib().eeg_tp_scatter_bwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]), _p(w_t, f32),
+                                    C.c_int64(E), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm), _p(dM, f32), _p(dw), _p(dh),
+                                    C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_bwd")
+    return dw, dh
+
+
+def sym_contract_bwd_x(lmax, nu, Cch, x, dout, T, n_nodes):
+    dx = torch.empty_like(x)
+    _begin("eeg_sym_contract_bwd_x")
+    _check(lib().eeg_sym_contract_bwd_x(C.c_int(lmax), C.c_int(nu), C.c_int(Cch), _p(x, f32), _p(dout, f32), _p(T, f32), _p(dx),
+                                        C.c_int64(n_nodes), _stream()), "eeg_sym_contract_bwd_x")
+    return dx
+
+
+def sc_weight_grad(x, dout, slot_tab, n_coef, D, Cch, n_nodes, t_ptr, t_row, t_val, n_wrows):
+    """-> dWflat [n_wrows, C]: coefficient gradient (table driven, sliced over nodes) folded back onto the weights."""
+    L = lib()
+    Z = L.eeg_sc_grad_slices()
+    dT = torch.empty(Z, Cch, n_coef, dtype=f32, device=x.device)
+    _begin("eeg_sc_coef_grad")
+    _check(L.eeg_sc_coef_grad(_p(x, f32), _p(dout, f32), _p(slot_tab, i32), C.c_int(n_coef), C.c_int(D), C.c_int(Cch), C.c_int64(n_nodes),
+                              _p(dT), _stream()), "eeg_sc_coef_grad")
+    dW = torch.empty(n_wrows, Cch, dtype=f32, device=x.device)
+    _begin("eeg_sc_coefficients_bwd")
+    _check(L.eeg_sc_coefficients_bwd(_p(t_ptr, i32), _p(t_row, i32), _p(t_val, f32), C.c_int(n_wrows), C.c_int(n_coef), _p(dT), C.c_int(Cch),
+                                     _p(dW), _stream()), "eeg_sc_coefficients_bwd")
+    return dW
+
+
+def sumsq(x, out):
+    """out[0] += sum(x^2) (global gradient norm for clipping)."""
+    _begin("eeg_sumsq")
+    _check(lib().eeg_sumsq(_p(x, f32), C.c_int64(x.numel()), _p(out, f32), _stream()), "eeg_sumsq")
+
+
+def adamw_step(p, g, m, v, vmax, lr, beta1, beta2, eps, weight_decay, step, gnorm_sq, max_norm, grad_scale):
+    """Fused AdamW (amsgrad when vmax is given) on flat fp32 buffers; clips by the global norm sqrt(gnorm_sq[0])."""
+    _begin("eeg_adamw_step")
+    _check(lib().eeg_adamw_step(_p(p, f32), _p(g, f32), _p(m, f32), _p(v, f32), _p(vmax, f32), C.c_int64(p.numel()), C.c_float(lr), C.c_float(beta1),
+                                C.c_float(beta2), C.c_float(eps), C.c_float(weight_decay), C.c_int(step), _p(gnorm_sq, f32), C.c_float(max_norm),
+                                C.c_float(grad_scale), _stream()), "eeg_adamw_step")

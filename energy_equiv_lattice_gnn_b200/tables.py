@@ -202,3 +202,23 @@ def sc_weight_map(lmax: int, correlation: int):
     return dict(row_ptr=row_ptr, col=cols.astype(np.int32), val=vals.astype(np.float32),
                 t_ptr=t_ptr, t_row=rows[ot].astype(np.int32), t_val=vals[ot].astype(np.float32),
                 w_off=w_off, n_wrows=n_wrows, n_coef=n_coef)
+
+
+def sc_slot_table(lmax: int, correlation: int) -> np.ndarray:
+    """int32 [n_coef, 4]: coefficient slot -> (output component, i, j, t) of the monomial it multiplies (-1 = absent);
+    padding slots are (-1,-1,-1,-1).  Used by the table-driven coefficient gradient (eeg_sc_coef_grad)."""
+    plan = sc_plan(lmax, correlation)
+    tab = -np.ones((plan["n_coef"], 4), dtype=np.int32)
+    o = 0
+    for ops_L in plan["ops"]:
+        for ops_M in ops_L:
+            for i, c1, js in ops_M:
+                if c1 >= 0:
+                    tab[c1] = (o, i, -1, -1)
+                for j, c2, ts in js:
+                    if c2 >= 0:
+                        tab[c2] = (o, i, j, -1)
+                    for t, c3 in ts:
+                        tab[c3] = (o, i, j, t)
+            o += 1
+    return tab

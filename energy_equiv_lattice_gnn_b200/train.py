@@ -1,0 +1,106 @@
+"""Training step of the reference harness (scripts/train_utils.py:38-64, scripts/train_main.py:89-100) on the B200 path:
+relative-MSE loss, explicit backward (autograd.py), one flat gradient all-reduce over NCCL/NVLink, global-norm clipping
+and a fused AdamW(amsgrad) kernel on one flat fp32 parameter buffer.  Lightning itself is out of scope; `Trainer` is the
+60-line stand-in SURVEY.md section 8(b) allows.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import native as nv
+
+
+def relative_mse_loss(pred: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    """scripts/train_utils.py:50-60: 100 * mean_g( mean_ij (pred - target)^2 / mean_ij target^2 )."""
+    mean_stiffness = target.pow(2).mean(dim=(1, 2))
+    stiffness_loss = torch.nn.functional.mse_loss(pred, target, reduction="none").mean(dim=(1, 2))
+    return 100 * (stiffness_loss / mean_stiffness).mean()
+
+
+def random_psd_targets(n: int, seed: int = 0) -> torch.Tensor:
+    """A = randn(6,6); C = ((A + A^T)/2)^2 / 6 (seeded)."""
+    g = torch.Generator().manual_seed(seed)
+    A = torch.randn(n, 6, 6, generator=g)
+    S = (A + A.transpose(1, 2)) / 2
+    return S @ S / 6
+
+
+class FlatAdamW:
+    """torch.optim.AdamW(lr, betas=(beta1, 0.999), eps, amsgrad, weight_decay) semantics (scripts/train_utils.py:38-44) +
+    Lightning's gradient_clip_val (clip_grad_norm_, scripts/train_main.py:91), fused over ONE flat fp32 buffer.
+
+    The model's parameters become views into `self.flat`; gradients are gathered into `self.grad` (also flat), which is
+    what the data-parallel all-reduce sends: one 0.89 MB message per step for the default model."""
+
+    def __init__(self, model: torch.nn.Module, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2, amsgrad=True,
+                 clip_norm: Optional[float] = 10.0):
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        dev = self.params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("FlatAdamW runs on the CUDA path only")
+        n = sum(p.numel() for p in self.params)
+        self.flat = torch.empty(n, dtype=torch.float32, device=dev)
+        self.grad = torch.zeros(n, dtype=torch.float32, device=dev)
+        off = 0
+        self.slices = []
+        for p in self.params:
+            k = p.numel()
+            self.flat[off:off + k].copy_(p.detach().reshape(-1))
+            p.data = self.flat[off:off + k].view_as(p)
+            p.grad = self.grad[off:off + k].view_as(p)
+            self.slices.append((off, k))
+            off += k
+        self.m = torch.zeros_like(self.flat)
+        self.v = torch.zeros_like(self.flat)
+        self.vmax = torch.zeros_like(self.flat) if amsgrad else None
+        self.gnorm_sq = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.lr, self.b1, self.b2, self.eps, self.wd, self.clip = lr, beta1, beta2, eps, weight_decay, clip_norm
+        self.t = 0
+
+    def zero_grad(self):
+        self.grad.zero_()
+
+    def gather_grads(self):
+        """Copy gradients that autograd left in separate tensors into the flat buffer (views are already in place)."""
+        for p, (off, k) in zip(self.params, self.slices):
+            if p.grad is not None and p.grad.data_ptr() != self.grad[off:off + k].data_ptr():
+                self.grad[off:off + k].copy_(p.grad.reshape(-1))
+                p.grad = self.grad[off:off + k].view_as(p)
+
+    def step(self, world_size: int = 1):
+        """Gradients in `self.grad` hold the SUM over ranks when world_size > 1 (all-reduce sum): scaled by 1/world here."""
+        self.t += 1
+        scale = 1.0 / world_size
+        gn = None
+        if self.clip is not None and self.clip > 0:
+            self.gnorm_sq.zero_()
+            nv.sumsq(self.grad, self.gnorm_sq)
+            gn = self.gnorm_sq
+        nv.adamw_step(self.flat, self.grad, self.m, self.v, self.vmax, self.lr, self.b1, self.b2, self.eps, self.wd, self.t, gn,
+                      self.clip or 0.0, scale)
+        return self
+
+
+class Trainer:
+    """training_step of scripts/train_utils.py:45-64 + optimizer step; DDP = one flat all-reduce (sum) per step."""
+
+    def __init__(self, model, lr=1e-3, beta1=0.9, eps=1e-8, weight_decay=1e-8, amsgrad=True, clip_norm=10.0, process_group=None):
+        self.model = model
+        self.opt = FlatAdamW(model, lr=lr, beta1=beta1, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad, clip_norm=clip_norm)
+        self.pg = process_group
+        self.world = torch.distributed.get_world_size(process_group) if (torch.distributed.is_available() and torch.distributed.is_initialized()) else 1
+
+    def training_step(self, batch) -> torch.Tensor:
+        self.model.train()
+        self.opt.zero_grad()
+        out = self.model(batch)["stiffness"]
+        loss = relative_mse_loss(out, batch.stiffness)
+        loss.backward()
+        self.opt.gather_grads()
+        if self.world > 1:
+            torch.distributed.all_reduce(self.opt.grad, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+        self.opt.step(self.world)
+        self.model._cache_bump()
+        return loss.detach()

@@ -117,6 +117,55 @@ int eeg_pool_tail_fwd(const float* o, const EegLayout* lo, const int32_t* graph_
                       int positive, int reduce, float* q_out /*[G,nq] or NULL*/, float* A_out /*[G,36] or NULL*/,
                       float* C_out /*[G,36]*/, int64_t G, void* stream);
 
+/* ====================================================================================================================
+ * Explicit backward ops (the reference differentiates the same graph with torch autograd over e3nn / torch_scatter /
+ * opt_einsum; scripts/train_utils.py:45-64 calls loss.backward()).  Input gradients of a linear are
+ * eeg_block_linear_fwd with transB = 1 (dX = dY W^T).  Gradient buffers marked "+=" must be zeroed by the caller.
+ * ==================================================================================================================== */
+
+/* dW_b[u,w] += scale_b * sum_{n,m} x[n,b,m,u] dy[n,b,m,w]  (transB = 1: stored as dW_b[w,u], torch.nn.Linear layout);
+ * dbias[w] += sum_n dy[n,0,0,w] (may be NULL).  in_ld / k_override may be NULL (row stride / K = mul of the layout). */
+int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
+                           const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
+                           const int32_t* k_override, float* dW, float* dbias, int64_t N, void* stream);
+/* out[c] += sum_r row_scale[r] * x[r*ld + c]   (row_scale may be NULL = 1): bias / embedding gradients */
+int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream);
+/* SiLU of the radial MLP (gnn/blocks.py:538-549): s = silu(a);  da = ds * silu'(a) */
+int eeg_silu_fwd(const float* a, float* s, int64_t n, void* stream);
+int eeg_silu_bwd(const float* a, const float* ds, float* da, int64_t n, void* stream);
+/* e3nn.nn.Gate backward (gnn/blocks.py:268-282): dz from z (layout lz) and dg (layout lg) */
+int eeg_gate_bwd(const float* z, const EegLayout* lz, const float* dg, const EegLayout* lg, int n_scalars, float act_const,
+                 float* dz, int64_t N, void* stream);
+/* Backward of eeg_pool_tail_fwd: A [G,36] is the forward's A_out; dC [G,36]; writes d_o [N, lo.stride] (all columns),
+ * dWq (same shape as Wq), dbias [q_0] (may be NULL); dq_ws [G,nq] and pooled_ws [G,npool] are workspaces. */
+int eeg_pool_tail_bwd(const float* o, const EegLayout* lo, const int32_t* graph_ptr, const float* Wq,
+                      const int32_t* host_qmul, const float* host_qscale, const float* P, int positive, int reduce,
+                      const float* A, const float* dC, float* d_o, float* dq_ws, float* pooled_ws, float* dWq, float* dbias,
+                      int64_t G, void* stream);
+/* Backward of eeg_tp_scatter_fwd: dw [E, n_paths*C] (edge-major, CSR order; fully written), dh [N,(lmax_in+1)^2,C] += */
+int eeg_tp_scatter_bwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
+                       int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, const float* dM,
+                       float* dw, float* dh, int64_t N, void* stream);
+/* Backward of eeg_sym_contract_fwd w.r.t. x (same coefficient table T as the forward) */
+int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, const float* dout, const float* T, float* dx, int64_t N,
+                           void* stream);
+/* Coefficient gradient: dT [eeg_sc_grad_slices()][C][n_coef] partial sums over node slices; slot_tab int32 [n_coef,4] =
+ * (output component, i, j, t) per slot (-1 absent).  eeg_sc_coefficients_bwd folds them onto the weights through the
+ * transposed (CSC) coefficient map: dW [n_wrows, C]. */
+int eeg_sc_grad_slices(void);
+int eeg_sc_coef_grad(const float* x, const float* dout, const int32_t* slot_tab, int n_coef, int D, int C, int64_t N, float* dT,
+                     void* stream);
+int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,
+                            const float* dT, int C, float* dW, void* stream);
+
+/* ---- optimizer step (scripts/train_utils.py:38-44 AdamW(amsgrad), scripts/train_main.py:91 gradient_clip_val) on flat
+ * fp32 buffers.  eeg_sumsq: out[0] += sum x^2.  eeg_adamw_step: g' = grad_scale * g clipped to max_norm by the global norm
+ * sqrt(gnorm_sq[0]) * grad_scale (gnorm_sq NULL or max_norm <= 0: no clipping); vmax NULL: plain AdamW. step counts from 1. */
+int eeg_sumsq(const float* x, int64_t n, float* out, void* stream);
+int eeg_adamw_step(float* p, const float* g, float* m, float* v, float* vmax, int64_t n, float lr, float beta1, float beta2,
+                   float eps, float weight_decay, int step, const float* gnorm_sq, float max_norm, float grad_scale,
+                   void* stream);
+
 #ifdef __cplusplus
 }
 #endif
