@@ -128,6 +128,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--lattices", type=int, default=1024, help="lattices per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (BASELINE.json configs[2])")
+    ap.add_argument("--train-lattices", type=int, default=512, help="lattices per GPU per training step")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -242,10 +244,47 @@ def main():
                 "traffic": None, "peak_source": peak_src, "ms_per_launch": top_ms, "share_of_step": top_ms / step_sum,
                 "algorithmic_bytes_per_launch": alg[top]["bytes"], "algorithmic_flops_per_launch": alg[top]["flops"],
                 "fp32_tflops_achieved": alg[top]["flops"] / (top_ms * 1e-3) / 1e12,
+                "fp32_tflops_peak_measured": 68.3, "fp32_peak_source": "tools/micro/ffma2_rate.cu on B200: 2.17 clk per FFMA2 per SMSP at 1.95 GHz",
                 "note": "kernel is fp32-FMA bound, not HBM bound (SURVEY.md App. C); bytes-based fraction reported as the contract asks"}
     kernels = {k: {"ms": round(v, 4), **({"GBps": round(alg[k]["bytes"] / v / 1e6, 1), "TFLOPs": round(alg[k]["flops"] / v / 1e9, 2)} if k in alg else {})}
                for k, v in sorted(kern.items(), key=lambda kv: -kv[1])}
 
+    # ---- training step (BASELINE.json configs[2]): fwd + loss + explicit backward + flat all-reduce + clip + AdamW(amsgrad)
+    train = None
+    if not args.no_train:
+        from energy_equiv_lattice_gnn_b200.train import Trainer, random_psd_targets
+        Gt = args.train_lattices
+        tb_, _ = synthetic_batch(range(10000 + Gt * rank, 10000 + Gt * rank + Gt), N_NODES)
+        tb_ = tb_.to(dev)
+        tb_.stiffness = random_psd_targets(Gt, seed=rank).to(dev)
+        torch.manual_seed(0)
+        tmodel = EnergyEquivGNN(params).to(dev)
+        trainer = Trainer(tmodel)
+        k_train = min(args.steps, 10)
+        l1 = native.launch_count
+        for _ in range(3):
+            trainer.training_step(tb_)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k_train):
+            loss = trainer.training_step(tb_)
+        e1.record()
+        barrier()
+        ms_t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if dist is not None:
+            dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+        native.start_profile()
+        trainer.training_step(tb_)
+        tprof = {k: sum(v) for k, v in native.stop_profile().items()}
+        ms_train = float(ms_t.item()) / k_train
+        train = {"metric": "lattices/sec training step (fwd + loss + backward + gradient all-reduce + clip + AdamW amsgrad)",
+                 "value": world * Gt / (ms_train * 1e-3), "unit": UNIT, "ms_per_step": ms_train, "lattices_per_gpu": Gt, "steps": k_train,
+                 "warmup": 3, "loss_last": float(loss), "gpu_launches_per_step": (native.launch_count - l1) // (k_train + 4),
+                 "allreduce_bytes_per_step": trainer.opt.grad.numel() * 4 if world > 1 else 0,
+                 "kernels_ms": {k: round(v, 4) for k, v in sorted(tprof.items(), key=lambda kv: -kv[1])[:16]},
+                 "workload": "BASELINE.json configs[2]: default hyper-parameters, random PSD targets, relative-MSE loss, no accumulation"}
+        del trainer, tmodel
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -258,6 +297,8 @@ def main():
             "e2e": {"value": world * G / (ms_e2e / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches_timed, "roofline": roofline, "kernels": kernels}
+    if train is not None:
+        line["train_step"] = train
     if world == 1 and not args.no_cpu_baseline:
         torch.set_num_threads(os.cpu_count() or 1)
         val, ms, thr = cpu_reference_run(3, 1, 2000)

@@ -77,6 +77,7 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
 
     # ---- tail: PositiveLayer, Mandel map, final linear, pooling
     qscale = [1.0 / math.sqrt(m) for m in model.rmul]
+    nv.set_tag('bwd.pool_tail')
     d_o, dWq, dbq = nv.pool_tail_bwd(sv["o"], model._lay_o, sv["gp"], head.linear.weight.detach(), model._qmul, qscale,
                                      head.linear.bias.numel(), model._tail_matrix(), _POSITIVE[model.params.positive_function],
                                      0 if model.params.global_reduction == "mean" else 1, sv["A"], dC.reshape(G, 36), G)
@@ -85,12 +86,15 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
     # ---- readout: linear_2, gate, linear_1
     w2off = np.concatenate(([0], np.cumsum([C * m for m in model.rmul])))[:-1].tolist()
     W2 = ro.linear_2.weight.detach()
+    nv.set_tag('bwd.readout.linear_2')
     grads[id(ro.linear_2.weight)] = nv.linear_wgrad(sv["g"], model._lay_g, d_o, model._lay_o, w2off, [sC] * nblk, W2.numel(), N)[0]
     dg = nv.block_linear(d_o, model._lay_o, W2, w2off, [sC] * nblk, model._lay_g, N, transB=True)
+    nv.set_tag('bwd.readout.gate')
     dz = nv.gate_bwd(sv["z"], model._lay_z, dg, model._lay_g, C, NORM2MOM_SILU, N)
     n_gates = C * lmax
     w1off = [0] + [C * (C + n_gates) + b * C * C for b in range(lmax)]
     W1 = ro.linear_1.weight.detach()
+    nv.set_tag('bwd.readout.linear_1')
     grads[id(ro.linear_1.weight)] = nv.linear_wgrad(sv["h_out"], model._lay_h, dz, model._lay_z, w1off, [sC] * nblk, W1.numel(), N)[0]
     dh = nv.block_linear(dz, model._lay_z, W1, w1off, [sC] * nblk, model._lay_h, N, transB=True)
 
@@ -112,12 +116,15 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         n_l = [ps["n_paths"] for ps in plan["passes"]]
         # h_new = product.linear(B) (+ h_in): gnn/blocks.py:488-490, gnn/model.py:95-96
         Wp = prod.linear.weight.detach()
+        nv.set_tag(f'bwd.L{i}.product_linear')
         grads[id(prod.linear.weight)] = nv.linear_wgrad(sv["B"][i], model._lay_h, dh, model._lay_h, offs, [sC] * nblk, Wp.numel(), N)[0]
         dB = nv.block_linear(dh, model._lay_h, Wp, offs, [sC] * nblk, model._lay_h, N, transB=True)
         # symmetric contraction
         x = sv["msg"][i]
         T = model._sc_table(i)
+        nv.set_tag(f'bwd.L{i}.sym_contract_dx')
         dmsg = nv.sym_contract_bwd_x(lmax, model.correlation, C, x, dB, T, N)
+        nv.set_tag(f'bwd.L{i}.sym_contract_dW')
         dWflat = nv.sc_weight_grad(x, dB, slot_tab, wmap["n_coef"], D, C, N, t_ptr, t_row, t_val, wmap["n_wrows"])
         row = 0
         for con in prod.symmetric_contractions.contractions.values():
@@ -129,25 +136,31 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         woff = np.concatenate(([0], np.cumsum([n * C * C for n in n_l])))[:-1].tolist()
         iscale = [1.0 / math.sqrt(n * C) for n in n_l]
         Wi = inter.linear.weight.detach()
+        nv.set_tag(f'bwd.L{i}.interaction_linear')
         gW, gb = nv.linear_wgrad(sv["M"][i], model._lay_M[i], dmsg, model._lay_h, woff, iscale, Wi.numel(), N, want_bias=C)
         grads[id(inter.linear.weight)] = gW
         grads[id(inter.linear.bias)] = gb
-        dM = nv.block_linear(dmsg, model._lay_h, Wi, woff, iscale, model._lay_M[i], N, transB=True)
+        inv_norm = 1.0 / model.agg_norm_const   # folded into dM so that the TP backward needs no rescaling pass
+        dM = nv.block_linear(dmsg, model._lay_h, Wi, woff, [sc * inv_norm for sc in iscale], model._lay_M[i], N, transB=True)
         # tensor product + scatter
+        nv.set_tag(f'bwd.L{i}.tp_scatter')
         dw, dhup = nv.tp_scatter_bwd(0 if i == 0 else lmax, lmax, C, sv["hup"][i], sv["Y"], sv["w"][i], sv["snd"], sv["row_ptr"],
-                                     1.0 / model.agg_norm_const, dM, len(plan["paths"]), N)
+                                     1.0, dM, len(plan["paths"]), N)
         # radial MLP
         lins = [m for m in inter.conv_tp_weights if isinstance(m, torch.nn.Linear)]
+        nv.set_tag(f'bwd.L{i}.radial_mlp')
         _mlp_backward(lins, sv["f"], dw, E, model._lay_f, model._lay_mlp, model._lay_w[i], grads)
         # linear_up
         Wu = inter.linear_up.weight.detach()
         uoff = [b * C * C for b in range(nb_in)]
+        nv.set_tag(f'bwd.L{i}.linear_up')
         grads[id(inter.linear_up.weight)] = nv.linear_wgrad(sv["h_in"][i], lay_in, dhup, lay_in, uoff, [sC] * nb_in, Wu.numel(), N)[0]
         dh_in = nv.block_linear(dhup, lay_in, Wu, uoff, [sC] * nb_in, lay_in, N, transB=True)
         dh = dh_in + dh if i > 0 else dh_in   # residual of layer i > 0 (gnn/model.py:95-96)
     # ---- node embedding: h0[n, c] = a[n] W[c] + b[c]
     emb = model.node_ft_embedding
     a = batch.node_attrs.to(torch.float32).reshape(-1).contiguous()
+    nv.set_tag('bwd.node_embed')
     grads[id(emb.weight)] = nv.colsum(dh, a).view_as(emb.weight)
     grads[id(emb.bias)] = nv.colsum(dh)
     return [grads.get(id(p)) if p.requires_grad else None for p in model.parameters()]

@@ -3,8 +3,8 @@
 //   eeg_sym_contract_bwd_x : dx[n,d,c] = sum_M dout[n,M,c] dP_M/dx_d, reverse-mode sweep of the same Horner tree and
 //                            coefficient stream as the forward (generated macro program, packed FFMA2 on node pairs)
 //   eeg_sc_coef_grad       : dT[z][c,slot] = sum_{n in node slice z} dout[n,M(slot),c] * monomial_slot(x[n,:,c])  (table
-//                            driven; a warp owns a few slots, lane = channel, fixed node order; EEG_SC_GRAD_SLICES
-//                            partial sums, no atomics: deterministic)
+//                            driven; a warp owns 8 slots, lane = channel, nodes staged in shared memory, fixed node
+//                            order; eeg_sc_grad_slices() partial sums, no atomics: deterministic)
 //   eeg_sc_coefficients_bwd: dW[k,c] = sum_slot A[slot,k] sum_z dT[z][c,slot]   (transpose of eeg_sc_coefficients)
 #include "eeg_common.cuh"
 #include "generated/scb_l3_nu3.cuh"
@@ -139,19 +139,23 @@ int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float
   return 0;
 }
 
-// ---- dT: a warp owns slots {w0, w0 + stride, ...} (at most SLOTS_PER_WARP), lane = channel chunk element --------------
-constexpr int CG_WARPS = 8, CG_SPW = 8;   // warps per CTA, slots per warp
+// ---- dT: a CTA owns 64 consecutive slots x one 32-channel chunk x one node slice; a warp owns 8 of the slots, lane =
+// channel.  Nodes are staged CG_NB at a time in shared memory ([x | dout][node][d][32 channels], coalesced 128-byte rows),
+// so a monomial factor is one conflict-free LDS; consecutive slots of the Horner order share dout_M x_i x_j, which is
+// recomputed only when (M, i, j) changes (warp-uniform test on the slot table held in registers).
+constexpr int CG_WARPS = 8, CG_SPW = 8, CG_NB = 4;
 
+template <int D>
 __global__ void __launch_bounds__(CG_WARPS * 32) k_sc_coef_grad(const float* __restrict__ x, const float* __restrict__ dout,
-                                                                 const int4* __restrict__ slot_tab, int n_coef, int D, int C,
+                                                                 const int4* __restrict__ slot_tab, int n_coef, int C,
                                                                  int64_t N, float* __restrict__ dT) {
+  extern __shared__ __align__(16) float cg_smem[];   // [2][CG_NB][D][32]
   const int64_t per = (N + gridDim.z - 1) / gridDim.z;
   const int64_t n_begin = blockIdx.z * per, n_end = n_begin + per < N ? n_begin + per : N;
   dT += (int64_t)blockIdx.z * C * n_coef;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int chunk = blockIdx.y;                       // 32-channel chunk
+  const int chunk = blockIdx.y;
   const int s0 = (blockIdx.x * CG_WARPS + warp) * CG_SPW;
-  if (s0 >= n_coef) return;
   int4 tab[CG_SPW];
   float acc[CG_SPW];
 #pragma unroll
@@ -160,18 +164,43 @@ __global__ void __launch_bounds__(CG_WARPS * 32) k_sc_coef_grad(const float* __r
     acc[q] = 0.f;
   }
   const int c = chunk * 32 + lane;
-  const float* xb = x + c;
-  const float* db = dout + c;
-  for (int64_t n = n_begin; n < n_end; ++n) {
-    const int64_t base = n * D * (int64_t)C;
+  float* xs = cg_smem;
+  float* ds = cg_smem + CG_NB * D * 32;
+  constexpr int ROWS = CG_NB * D;                                // staged rows per tensor
+  constexpr int PER_WARP = (2 * ROWS + CG_WARPS - 1) / CG_WARPS;   // rows each warp copies per batch
+  for (int64_t nb = n_begin; nb < n_end; nb += CG_NB) {
+    float v[PER_WARP];   // every load of the batch is in flight before the first store
 #pragma unroll
-    for (int q = 0; q < CG_SPW; ++q) {
-      const int4 e = tab[q];   // (M, i, j, t); -1 = absent
-      if (e.x < 0) continue;   // warp-uniform
-      float v = __ldg(db + base + (int64_t)e.x * C) * __ldg(xb + base + (int64_t)e.y * C);
-      if (e.z >= 0) v *= __ldg(xb + base + (int64_t)e.z * C);
-      if (e.w >= 0) v *= __ldg(xb + base + (int64_t)e.w * C);
-      acc[q] += v;
+    for (int u = 0; u < PER_WARP; ++u) {
+      const int r = warp + u * CG_WARPS;
+      const int which = r >= ROWS, rr = which ? r - ROWS : r;
+      const int64_t n = nb + rr / D;
+      v[u] = (r < 2 * ROWS && n < n_end) ? __ldg((which ? dout : x) + (n * D + rr % D) * (int64_t)C + c) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < PER_WARP; ++u) {
+      const int r = warp + u * CG_WARPS;
+      if (r < 2 * ROWS) (r >= ROWS ? ds + (r - ROWS) * 32 : xs + r * 32)[lane] = v[u];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < CG_NB; ++k) {
+      const float* xk = xs + k * D * 32 + lane;
+      const float* dk = ds + k * D * 32 + lane;
+      int pm = -2, pi = -2, pj = -2;
+      float P = 0.f;
+#pragma unroll
+      for (int q = 0; q < CG_SPW; ++q) {
+        const int4 e = tab[q];   // (M, i, j, t); -1 = absent (warp-uniform)
+        if (e.x < 0) continue;
+        if (e.x != pm || e.y != pi || e.z != pj) {
+          P = dk[e.x * 32] * xk[e.y * 32];
+          if (e.z >= 0) P *= xk[e.z * 32];
+          pm = e.x; pi = e.y; pj = e.z;
+        }
+        acc[q] += e.w >= 0 ? P * xk[e.w * 32] : P;
+      }
     }
   }
 #pragma unroll
@@ -213,7 +242,10 @@ extern "C" int eeg_sc_coef_grad(const float* x, const float* dout, const int32_t
   EEG_REQUIRE(C > 0 && C % 32 == 0, "eeg_sc_coef_grad: C must be a multiple of 32");
   if (n_coef == 0) return 0;
   dim3 grid(eeg_div_up(n_coef, CG_WARPS * CG_SPW), C / 32, eeg_sc_grad_slices());   // N == 0: slices are written as zeros
-  k_sc_coef_grad<<<grid, CG_WARPS * 32, 0, (cudaStream_t)stream>>>(x, dout, reinterpret_cast<const int4*>(slot_tab), n_coef, D, C, N, dT);
+  const size_t smem = (size_t)2 * CG_NB * D * 32 * sizeof(float);
+  EEG_REQUIRE(D == 25 || D == 16, "eeg_sc_coef_grad: D must be 25 (lmax 4) or 16 (lmax 3), got %d", D);
+  if (D == 25) k_sc_coef_grad<25><<<grid, CG_WARPS * 32, smem, (cudaStream_t)stream>>>(x, dout, reinterpret_cast<const int4*>(slot_tab), n_coef, C, N, dT);
+  else k_sc_coef_grad<16><<<grid, CG_WARPS * 32, smem, (cudaStream_t)stream>>>(x, dout, reinterpret_cast<const int4*>(slot_tab), n_coef, C, N, dT);
   EEG_CHECK_LAUNCH("eeg_sc_coef_grad");
   return 0;
 }

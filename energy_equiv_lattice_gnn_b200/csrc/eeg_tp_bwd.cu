@@ -77,9 +77,11 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__
       __syncwarp();
       float* dwp = dw + (int64_t)e * I::NPATHS * C + c;
       I::run(x, reinterpret_cast<const float4*>(Gs), w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane, wstride, dMp, C, dwp, dx);
-      // fold 1 / agg_norm_const
+      // fold 1 / agg_norm_const (callers that pre-scale dM pass inv_norm = 1 and skip the read-modify-write of dw)
+      if (inv_norm != 1.0f) {
 #pragma unroll
-      for (int p = 0; p < I::NPATHS; ++p) dwp[(int64_t)p * C] *= inv_norm;
+        for (int p = 0; p < I::NPATHS; ++p) dwp[(int64_t)p * C] *= inv_norm;
+      }
 #pragma unroll
       for (int d = 0; d < DIN; ++d) atomicAdd(dh + ((int64_t)s * DIN + d) * C + c, dx[d] * inv_norm);
     }

@@ -27,6 +27,19 @@ def random_psd_targets(n: int, seed: int = 0) -> torch.Tensor:
     return S @ S / 6
 
 
+def sync_gradients(flat_grad: torch.Tensor, process_group=None) -> int:
+    """Data-parallel gradient exchange: ONE all-reduce (sum) of the flat gradient buffer (NCCL over NVLink on the GPU
+    path, gloo in the CPU tests).  Returns the world size; the 1/world of DDP's gradient mean is folded into the
+    optimizer kernel (`FlatAdamW.step(world)`).  Equal-sized shards make this identical to the single-process gradient
+    of the global-mean loss (Lightning DDP + per-rank mean loss, scripts/train_utils.py:57-60)."""
+    if not (torch.distributed.is_available() and torch.distributed.is_initialized()):
+        return 1
+    world = torch.distributed.get_world_size(process_group)
+    if world > 1:
+        torch.distributed.all_reduce(flat_grad, op=torch.distributed.ReduceOp.SUM, group=process_group)
+    return world
+
+
 class FlatAdamW:
     """torch.optim.AdamW(lr, betas=(beta1, 0.999), eps, amsgrad, weight_decay) semantics (scripts/train_utils.py:38-44) +
     Lightning's gradient_clip_val (clip_grad_norm_, scripts/train_main.py:91), fused over ONE flat fp32 buffer.
@@ -72,6 +85,7 @@ class FlatAdamW:
     def step(self, world_size: int = 1):
         """Gradients in `self.grad` hold the SUM over ranks when world_size > 1 (all-reduce sum): scaled by 1/world here."""
         self.t += 1
+        nv.set_tag('optimizer')
         scale = 1.0 / world_size
         gn = None
         if self.clip is not None and self.clip > 0:
@@ -90,7 +104,6 @@ class Trainer:
         self.model = model
         self.opt = FlatAdamW(model, lr=lr, beta1=beta1, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad, clip_norm=clip_norm)
         self.pg = process_group
-        self.world = torch.distributed.get_world_size(process_group) if (torch.distributed.is_available() and torch.distributed.is_initialized()) else 1
 
     def training_step(self, batch) -> torch.Tensor:
         self.model.train()
@@ -99,8 +112,7 @@ class Trainer:
         loss = relative_mse_loss(out, batch.stiffness)
         loss.backward()
         self.opt.gather_grads()
-        if self.world > 1:
-            torch.distributed.all_reduce(self.opt.grad, op=torch.distributed.ReduceOp.SUM, group=self.pg)
-        self.opt.step(self.world)
+        world = sync_gradients(self.opt.grad, self.pg)
+        self.opt.step(world)
         self.model._cache_bump()
         return loss.detach()
