@@ -100,11 +100,9 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
 
     wmap = model._wmap
     dev = dC.device
-    slot_tab = _static(model, "slot_tab", lambda: torch.tensor(tb.sc_slot_table(lmax, model.correlation), device=dev))
     t_ptr = _static(model, "t_ptr", lambda: torch.tensor(wmap["t_ptr"], device=dev))
     t_row = _static(model, "t_row", lambda: torch.tensor(wmap["t_row"], device=dev))
     t_val = _static(model, "t_val", lambda: torch.tensor(wmap["t_val"], device=dev))
-    D = (lmax + 1) ** 2
     offs = [b * C * C for b in range(nblk)]
 
     for i in range(len(head.layers) - 1, -1, -1):
@@ -125,7 +123,7 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         nv.set_tag(f'bwd.L{i}.sym_contract_dx')
         dmsg = nv.sym_contract_bwd_x(lmax, model.correlation, C, x, dB, T, N)
         nv.set_tag(f'bwd.L{i}.sym_contract_dW')
-        dWflat = nv.sc_weight_grad(x, dB, slot_tab, wmap["n_coef"], D, C, N, t_ptr, t_row, t_val, wmap["n_wrows"])
+        dWflat = nv.sc_weight_grad(lmax, model.correlation, x, dB, wmap["n_coef"], C, N, t_ptr, t_row, t_val, wmap["n_wrows"])
         row = 0
         for con in prod.symmetric_contractions.contractions.values():
             for nu in range(1, model.correlation + 1):

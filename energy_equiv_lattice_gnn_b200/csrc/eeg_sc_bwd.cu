@@ -1,11 +1,8 @@
 // Symmetric contraction (gnn/mace.py:112-277), backward.  The reference differentiates its einsum chain with autograd;
-// here the two gradients are explicit:
+// here the gradients are explicit:
 //   eeg_sym_contract_bwd_x : dx[n,d,c] = sum_M dout[n,M,c] dP_M/dx_d, reverse-mode sweep of the same Horner tree and
 //                            coefficient stream as the forward (generated macro program, packed FFMA2 on node pairs)
-//   eeg_sc_coef_grad       : dT[z][c,slot] = sum_{n in node slice z} dout[n,M(slot),c] * monomial_slot(x[n,:,c])  (table
-//                            driven; a warp owns 8 slots, lane = channel, nodes staged in shared memory, fixed node
-//                            order; eeg_sc_grad_slices() partial sums, no atomics: deterministic)
-//   eeg_sc_coefficients_bwd: dW[k,c] = sum_slot A[slot,k] sum_z dT[z][c,slot]   (transpose of eeg_sc_coefficients)
+// (weight gradient: eeg_sc_wgrad.cu)
 #include "eeg_common.cuh"
 #include "generated/scb_l3_nu3.cuh"
 #include "generated/scb_l4_nu3.cuh"
@@ -139,92 +136,6 @@ int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float
   return 0;
 }
 
-// ---- dT: a CTA owns 64 consecutive slots x one 32-channel chunk x one node slice; a warp owns 8 of the slots, lane =
-// channel.  Nodes are staged CG_NB at a time in shared memory ([x | dout][node][d][32 channels], coalesced 128-byte rows),
-// so a monomial factor is one conflict-free LDS; consecutive slots of the Horner order share dout_M x_i x_j, which is
-// recomputed only when (M, i, j) changes (warp-uniform test on the slot table held in registers).
-constexpr int CG_WARPS = 8, CG_SPW = 8, CG_NB = 4;
-
-template <int D>
-__global__ void __launch_bounds__(CG_WARPS * 32) k_sc_coef_grad(const float* __restrict__ x, const float* __restrict__ dout,
-                                                                 const int4* __restrict__ slot_tab, int n_coef, int C,
-                                                                 int64_t N, float* __restrict__ dT) {
-  extern __shared__ __align__(16) float cg_smem[];   // [2][CG_NB][D][32]
-  const int64_t per = (N + gridDim.z - 1) / gridDim.z;
-  const int64_t n_begin = blockIdx.z * per, n_end = n_begin + per < N ? n_begin + per : N;
-  dT += (int64_t)blockIdx.z * C * n_coef;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int chunk = blockIdx.y;
-  const int s0 = (blockIdx.x * CG_WARPS + warp) * CG_SPW;
-  int4 tab[CG_SPW];
-  float acc[CG_SPW];
-#pragma unroll
-  for (int q = 0; q < CG_SPW; ++q) {
-    tab[q] = s0 + q < n_coef ? __ldg(slot_tab + s0 + q) : make_int4(-1, -1, -1, -1);
-    acc[q] = 0.f;
-  }
-  const int c = chunk * 32 + lane;
-  float* xs = cg_smem;
-  float* ds = cg_smem + CG_NB * D * 32;
-  constexpr int ROWS = CG_NB * D;                                // staged rows per tensor
-  constexpr int PER_WARP = (2 * ROWS + CG_WARPS - 1) / CG_WARPS;   // rows each warp copies per batch
-  for (int64_t nb = n_begin; nb < n_end; nb += CG_NB) {
-    float v[PER_WARP];   // every load of the batch is in flight before the first store
-#pragma unroll
-    for (int u = 0; u < PER_WARP; ++u) {
-      const int r = warp + u * CG_WARPS;
-      const int which = r >= ROWS, rr = which ? r - ROWS : r;
-      const int64_t n = nb + rr / D;
-      v[u] = (r < 2 * ROWS && n < n_end) ? __ldg((which ? dout : x) + (n * D + rr % D) * (int64_t)C + c) : 0.f;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int u = 0; u < PER_WARP; ++u) {
-      const int r = warp + u * CG_WARPS;
-      if (r < 2 * ROWS) (r >= ROWS ? ds + (r - ROWS) * 32 : xs + r * 32)[lane] = v[u];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < CG_NB; ++k) {
-      const float* xk = xs + k * D * 32 + lane;
-      const float* dk = ds + k * D * 32 + lane;
-      int pm = -2, pi = -2, pj = -2;
-      float P = 0.f;
-#pragma unroll
-      for (int q = 0; q < CG_SPW; ++q) {
-        const int4 e = tab[q];   // (M, i, j, t); -1 = absent (warp-uniform)
-        if (e.x < 0) continue;
-        if (e.x != pm || e.y != pi || e.z != pj) {
-          P = dk[e.x * 32] * xk[e.y * 32];
-          if (e.z >= 0) P *= xk[e.z * 32];
-          pm = e.x; pi = e.y; pj = e.z;
-        }
-        acc[q] += e.w >= 0 ? P * xk[e.w * 32] : P;
-      }
-    }
-  }
-#pragma unroll
-  for (int q = 0; q < CG_SPW; ++q)
-    if (s0 + q < n_coef) dT[(int64_t)c * n_coef + s0 + q] = acc[q];
-}
-
-__global__ void k_sc_coefficients_bwd(const int32_t* __restrict__ tp, const int32_t* __restrict__ trow, const float* __restrict__ tval,
-                                      int n_wrows, int n_coef, const float* __restrict__ dT, int n_slices, int C,
-                                      float* __restrict__ dW) {
-  const int k = blockIdx.x * blockDim.y + threadIdx.y;
-  if (k >= n_wrows) return;
-  for (int c = threadIdx.x; c < C; c += 32) {
-    float s = 0.f;
-    for (int q = tp[k]; q < tp[k + 1]; ++q) {
-      const int64_t o = (int64_t)c * n_coef + __ldg(trow + q);
-      float d = 0.f;
-      for (int z = 0; z < n_slices; ++z) d += __ldg(dT + (int64_t)z * C * n_coef + o);
-      s = fmaf(__ldg(tval + q), d, s);
-    }
-    dW[(int64_t)k * C + c] = s;
-  }
-}
-
 }  // namespace
 
 extern "C" int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, const float* dout, const float* T, float* dx,
@@ -233,29 +144,4 @@ extern "C" int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, c
   EEG_REQUIRE(C > 0 && C % CH == 0, "eeg_sym_contract_bwd_x: C must be a multiple of %d", CH);
   if (N == 0) return 0;
   return lmax == 4 ? launch_bwd_x<4>(C, x, dout, T, dx, N, (cudaStream_t)stream) : launch_bwd_x<3>(C, x, dout, T, dx, N, (cudaStream_t)stream);
-}
-
-extern "C" int eeg_sc_grad_slices(void) { return 16; }
-
-extern "C" int eeg_sc_coef_grad(const float* x, const float* dout, const int32_t* slot_tab, int n_coef, int D, int C, int64_t N,
-                                float* dT, void* stream) {
-  EEG_REQUIRE(C > 0 && C % 32 == 0, "eeg_sc_coef_grad: C must be a multiple of 32");
-  if (n_coef == 0) return 0;
-  dim3 grid(eeg_div_up(n_coef, CG_WARPS * CG_SPW), C / 32, eeg_sc_grad_slices());   // N == 0: slices are written as zeros
-  const size_t smem = (size_t)2 * CG_NB * D * 32 * sizeof(float);
-  EEG_REQUIRE(D == 25 || D == 16, "eeg_sc_coef_grad: D must be 25 (lmax 4) or 16 (lmax 3), got %d", D);
-  if (D == 25) k_sc_coef_grad<25><<<grid, CG_WARPS * 32, smem, (cudaStream_t)stream>>>(x, dout, reinterpret_cast<const int4*>(slot_tab), n_coef, C, N, dT);
-  else k_sc_coef_grad<16><<<grid, CG_WARPS * 32, smem, (cudaStream_t)stream>>>(x, dout, reinterpret_cast<const int4*>(slot_tab), n_coef, C, N, dT);
-  EEG_CHECK_LAUNCH("eeg_sc_coef_grad");
-  return 0;
-}
-
-extern "C" int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,
-                                       const float* dT, int C, float* dW, void* stream) {
-  const int n_slices = eeg_sc_grad_slices();
-  if (n_wrows == 0) return 0;
-  dim3 block(32, 8), grid(eeg_div_up(n_wrows, 8));
-  k_sc_coefficients_bwd<<<grid, block, 0, (cudaStream_t)stream>>>(t_ptr, t_row, t_val, n_wrows, n_coef, dT, n_slices, C, dW);
-  EEG_CHECK_LAUNCH("eeg_sc_coefficients_bwd");
-  return 0;
 }

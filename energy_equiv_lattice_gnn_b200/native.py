@@ -368,13 +368,13 @@ def sym_contract_bwd_x(lmax, nu, Cch, x, dout, T, n_nodes):
     return dx
 
 
-def sc_weight_grad(x, dout, slot_tab, n_coef, D, Cch, n_nodes, t_ptr, t_row, t_val, n_wrows):
-    """-> dWflat [n_wrows, C]: coefficient gradient (table driven, sliced over nodes) folded back onto the weights."""
+def sc_weight_grad(lmax, nu, x, dout, n_coef, Cch, n_nodes, t_ptr, t_row, t_val, n_wrows):
+    """-> dWflat [n_wrows, C]: coefficient gradient (generated program, sliced over nodes) folded back onto the weights."""
     L = lib()
     Z = L.eeg_sc_grad_slices()
-    dT = torch.empty(Z, Cch, n_coef, dtype=f32, device=x.device)
+    dT = torch.empty(Z, n_coef, Cch, dtype=f32, device=x.device)
     _begin("eeg_sc_coef_grad")
-    _check(L.eeg_sc_coef_grad(_p(x, f32), _p(dout, f32), _p(slot_tab, i32), C.c_int(n_coef), C.c_int(D), C.c_int(Cch), C.c_int64(n_nodes),
+    _check(L.eeg_sc_coef_grad(C.c_int(lmax), C.c_int(nu), C.c_int(Cch), _p(x, f32), _p(dout, f32), C.c_int(n_coef), C.c_int64(n_nodes),
                               _p(dT), _stream()), "eeg_sc_coef_grad")
     dW = torch.empty(n_wrows, Cch, dtype=f32, device=x.device)
     _begin("eeg_sc_coefficients_bwd")

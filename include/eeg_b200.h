@@ -149,14 +149,14 @@ int eeg_tp_scatter_bwd(int lmax_in, int lmax, int C, const float* h, const float
 /* Backward of eeg_sym_contract_fwd w.r.t. x (same coefficient table T as the forward) */
 int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, const float* dout, const float* T, float* dx, int64_t N,
                            void* stream);
-/* Coefficient gradient: dT [eeg_sc_grad_slices()][C][n_coef] partial sums over node slices; slot_tab int32 [n_coef,4] =
- * (output component, i, j, t) per slot (-1 absent).  eeg_sc_coefficients_bwd folds them onto the weights through the
- * transposed (CSC) coefficient map: dW [n_wrows, C]. */
+/* Coefficient gradient: dT [eeg_sc_grad_slices()][n_coef][C] partial sums over node slices (fixed order: deterministic);
+ * n_coef must equal the slot count of the compiled (lmax, nu) program.  eeg_sc_coefficients_bwd folds them onto the
+ * weights through the transposed (CSC) coefficient map: dW [n_wrows, C]; it sums the slices into slice 0 in place first
+ * (dT is scratch). */
 int eeg_sc_grad_slices(void);
-int eeg_sc_coef_grad(const float* x, const float* dout, const int32_t* slot_tab, int n_coef, int D, int C, int64_t N, float* dT,
-                     void* stream);
+int eeg_sc_coef_grad(int lmax, int nu, int C, const float* x, const float* dout, int n_coef, int64_t N, float* dT, void* stream);
 int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,
-                            const float* dT, int C, float* dW, void* stream);
+                            float* dT, int C, float* dW, void* stream);
 
 /* ---- optimizer step (scripts/train_utils.py:38-44 AdamW(amsgrad), scripts/train_main.py:91 gradient_clip_val) on flat
  * fp32 buffers.  eeg_sumsq: out[0] += sum x^2.  eeg_adamw_step: g' = grad_scale * g clipped to max_norm by the global norm

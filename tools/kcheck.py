@@ -148,12 +148,55 @@ def check_linear(N=30720, C=32, lmax=4, npaths=(5, 8, 10, 10, 9), seed=0):
     print("LINEAR", "OK" if ok else "FAIL", "(EEG_LINEAR=%s)" % os.environ.get("EEG_LINEAR", "tc"))
 
 
+def check_scw(N=15360, C=32, lmax=4):
+    """Symmetric-contraction weight gradient: dT program and the fold onto the weights, timed separately; dT vs fp64."""
+    import ctypes as ct
+    from energy_equiv_lattice_gnn_b200 import tables as tb
+    wmap = tb.sc_weight_map(lmax, 3)
+    n_coef, D = wmap["n_coef"], (lmax + 1) ** 2
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(N, D, C, generator=g).to(dev)
+    dout = torch.randn(N, D, C, generator=g).to(dev)
+    L = nv.lib()
+    Z = L.eeg_sc_grad_slices()
+    dT = torch.empty(Z, n_coef, C, device=dev)
+    t_ptr, t_row, t_val = (torch.tensor(wmap[k], device=dev) for k in ("t_ptr", "t_row", "t_val"))
+    dW = torch.empty(wmap["n_wrows"], C, device=dev)
+    st = lambda: ct.c_void_p(torch.cuda.current_stream().cuda_stream)  # noqa: E731
+    f1 = lambda: L.eeg_sc_coef_grad(ct.c_int(lmax), ct.c_int(3), ct.c_int(C), ct.c_void_p(x.data_ptr()), ct.c_void_p(dout.data_ptr()),  # noqa: E731
+                                    ct.c_int(n_coef), ct.c_int64(N), ct.c_void_p(dT.data_ptr()), st())
+    f2 = lambda: L.eeg_sc_coefficients_bwd(ct.c_void_p(t_ptr.data_ptr()), ct.c_void_p(t_row.data_ptr()), ct.c_void_p(t_val.data_ptr()),  # noqa: E731
+                                           ct.c_int(wmap["n_wrows"]), ct.c_int(n_coef), ct.c_void_p(dT.data_ptr()), ct.c_int(C),
+                                           ct.c_void_p(dW.data_ptr()), st())
+    assert f1() == 0 and f2() == 0
+    torch.cuda.synchronize()
+    tab = torch.tensor(tb.sc_slot_table(lmax, 3))
+    n_chk = min(N, 512)
+    xd, gd = x[:n_chk].double().cpu(), dout[:n_chk].double().cpu()
+    one = torch.ones(n_chk, 1, C, dtype=torch.float64)
+    xe = torch.cat([xd, one], 1)  # index -1 -> ones row
+    ok_rows = tab[:, 0] >= 0
+    M, i, j, t = (tab[:, k].clamp(min=-1) for k in range(4))
+    ref = gd[:, M.clamp(min=0)] * xe[:, i] * xe[:, j] * xe[:, t]
+    ref = (ref * ok_rows[None, :, None]).sum(0)
+    x2 = x[:n_chk].contiguous(); d2 = dout[:n_chk].contiguous()
+    dT2 = torch.empty_like(dT)
+    L.eeg_sc_coef_grad(ct.c_int(lmax), ct.c_int(3), ct.c_int(C), ct.c_void_p(x2.data_ptr()), ct.c_void_p(d2.data_ptr()), ct.c_int(n_coef),
+                       ct.c_int64(n_chk), ct.c_void_p(dT2.data_ptr()), st())
+    got = dT2.double().sum(0).cpu()
+    err = float((got - ref).abs().max() / ref.abs().max())
+    print(f"scw lmax={lmax} N={N} C={C} n_coef={n_coef} n_wrows={wmap['n_wrows']} nnz={len(wmap['t_row'])}: dT rel err {err:.2e}  "
+          f"coef_grad {timeit(f1, n=10)*1e3:.1f} us  coefficients_bwd {timeit(f2, n=10)*1e3:.1f} us", flush=True)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "radial"
     if what == "linear":
         check_linear()
     if what == "sc":
         check_sc(int(sys.argv[2]) if len(sys.argv) > 2 else 30720, 32, int(sys.argv[3]) if len(sys.argv) > 3 else 4)
+    if what == "scw":
+        check_scw(int(sys.argv[2]) if len(sys.argv) > 2 else 15360, 32, int(sys.argv[3]) if len(sys.argv) > 3 else 4)
     if what == "sc_compare":
         import glob
         for lmax in (3, 4):
