@@ -163,6 +163,8 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # the version banner goes to stdout, which must hold exactly one JSON line
         dist.init_process_group("nccl", device_id=dev)
     from energy_equiv_lattice_gnn_b200 import EnergyEquivGNN, native
     from energy_equiv_lattice_gnn_b200.data import synthetic_batch
