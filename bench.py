@@ -126,7 +126,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--lattices", type=int, default=1024, help="lattices per GPU per step")
+    ap.add_argument("--lattices", type=int, default=None, help="lattices per GPU per step (default: the config's)")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 4, 5],
+                    help="BASELINE.json workload: 2 = headline (1024 x 30-node lattices, default model); 4 = lmax 3, C = 128, 256 lattices; "
+                         "5 = 1024 x 216-node lattices (inference only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (BASELINE.json configs[2])")
     ap.add_argument("--train-lattices", type=int, default=512, help="lattices per GPU per training step")
@@ -134,11 +137,22 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # workload table: lattices/GPU, nodes/lattice, first seed, model overrides, BASELINE.json index
+    cfg = {2: (1024, 30, 2000, {}, "default hyper-parameters (lmax=4, 32 channels, correlation 3, 2 message passes)", 1),
+           4: (256, 30, 20000, dict(lmax=3, hidden_irreps="128x0e+128x1o+128x2e+128x3o", readout_irreps="64x0e+64x1o+64x2e+64x3o"),
+               "lmax=3, 128 channels, correlation 3, 2 message passes", 3),
+           5: (1024, 216, 30000, {}, "default hyper-parameters, 216-node lattices (32 distinct lattices tiled 32x per batch)", 4)}[args.config]
+    if args.lattices is None:
+        args.lattices = cfg[0]
+    n_nodes_lat = cfg[1]
     config = {"workload": f"EnergyEquivGNN inference fwd+stiffness, batch {args.lattices} synthetic lattices/GPU "
-                          f"({N_NODES} nodes, {2 * N_NODES} struts, {4 * N_NODES} directed edges each), default hyper-parameters "
-                          "(lmax=4, 32 channels, correlation 3, 2 message passes), fp32 [BASELINE.json configs[1]]",
-              "lattices_per_gpu": args.lattices, "nodes_per_lattice": N_NODES, "edges_per_lattice": 4 * N_NODES,
-              "l2": "per-step working set (~2.7 GB of intermediates at 1024 lattices) >> 126 MB L2; inputs rotate over 2 distinct batches"}
+                          f"({n_nodes_lat} nodes, {2 * n_nodes_lat} struts, {4 * n_nodes_lat} directed edges each), {cfg[4]}, "
+                          f"fp32 [BASELINE.json configs[{cfg[5]}]]",
+              "lattices_per_gpu": args.lattices, "nodes_per_lattice": n_nodes_lat, "edges_per_lattice": 4 * n_nodes_lat,
+              "l2": "per-step working set (GBs of intermediates) >> 126 MB L2; inputs rotate over 2 distinct batches"}
+    if args.config != 2:
+        args.no_train = True
+        args.no_cpu_baseline = True
 
     if args.impl == "reference":
         if rank != 0:
@@ -175,11 +189,17 @@ def main():
     host_batches = []
     rmax = 0.0
     for k in range(2):
-        seed0 = 2000 + (2 * rank + k) * G
-        b, r = synthetic_batch(range(seed0, seed0 + G), N_NODES)
+        if args.config == 5:   # 216-node lattices are slow to generate on the host: 32 distinct ones, tiled
+            from energy_equiv_lattice_gnn_b200.data import collate, synthetic_lattice
+            distinct = [synthetic_lattice(cfg[2] + (2 * rank + k) * 32 + i, n_nodes_lat) for i in range(min(32, G))]
+            data = [distinct[i % len(distinct)] for i in range(G)]
+            b, r = collate(data), max(float(d.edge_attr.max()) for d in distinct)
+        else:
+            seed0 = cfg[2] + (2 * rank + k) * G
+            b, r = synthetic_batch(range(seed0, seed0 + G), n_nodes_lat)
         host_batches.append(b.pin_memory())
         rmax = max(rmax, r)
-    params = default_params(max_edge_radius=rmax)
+    params = default_params(max_edge_radius=rmax, **cfg[3])
     torch.manual_seed(0)
     model = EnergyEquivGNN(params).to(dev).eval()
     dev_batches = [b.to(dev) for b in host_batches]

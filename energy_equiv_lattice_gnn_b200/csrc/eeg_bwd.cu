@@ -245,24 +245,36 @@ __global__ void __launch_bounds__(128) k_pool_tail_bwd(const float* __restrict__
 }
 
 // dWq_b[u][w] = scale_b sum_g sum_m pooled[g][b][m][u] dq[g][b][w][m];  dbias[w] = sum_g dq[g][0][w][0]
-__global__ void k_tail_wgrad(const float* __restrict__ pooled, const float* __restrict__ dq, float* __restrict__ dWq,
-                             float* __restrict__ dbias, int64_t G, TailBwdParams P, int n_w) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(128) k_tail_wgrad(const float* __restrict__ pooled, const float* __restrict__ dq,
+                                                     float* __restrict__ dWq, float* __restrict__ dbias, int64_t G, TailBwdParams P,
+                                                     int n_w) {
+  // one CTA per output element; threads stride over the graphs, fixed-order tree reduction (deterministic)
+  const int i = blockIdx.x;
+  float s = 0.f;
+  float scale = 1.f;
   if (i < n_w) {
     int b = -1;
     for (int k = 0; k < P.lo.n_blocks; ++k)
       if (P.qmul[k] > 0 && i >= P.woff[k]) b = k;
     const int rows = P.lo.rows[b], mul = P.lo.mul[b], r = i - P.woff[b];
     const int u = r / P.qmul[b], w = r % P.qmul[b];
-    float s = 0.f;
-    for (int64_t g = 0; g < G; ++g)
-      for (int m = 0; m < rows; ++m) s = fmaf(pooled[g * P.npool + P.poff[b] + m * mul + u], dq[g * P.nq + P.qoff[b] + w * rows + m], s);
-    dWq[i] = s * P.qscale[b];
-  } else if (dbias != nullptr && i < n_w + P.qmul[0]) {
+    const float* pp = pooled + P.poff[b] + u;
+    const float* qq = dq + P.qoff[b] + w * rows;
+    for (int64_t g = threadIdx.x; g < G; g += blockDim.x)
+      for (int m = 0; m < rows; ++m) s = fmaf(pp[g * P.npool + m * mul], qq[g * P.nq + m], s);
+    scale = P.qscale[b];
+  } else {
     const int w = i - n_w;
-    float s = 0.f;
-    for (int64_t g = 0; g < G; ++g) s += dq[g * P.nq + P.qoff[0] + w * P.lo.rows[0]];
-    dbias[w] = s;
+    for (int64_t g = threadIdx.x; g < G; g += blockDim.x) s += dq[g * P.nq + P.qoff[0] + w * P.lo.rows[0]];
+  }
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  __shared__ float ws[4];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const float t = (ws[0] + ws[1]) + (ws[2] + ws[3]);
+    if (i < n_w) dWq[i] = t * scale;
+    else dbias[i - n_w] = t;
   }
 }
 
@@ -384,7 +396,7 @@ extern "C" int eeg_pool_tail_bwd(const float* o, const EegLayout* lo, const int3
   k_pool_tail_bwd<<<(unsigned)G, 128, smem, (cudaStream_t)stream>>>(o, graph_ptr, Wq, P, A, dC, d_o, dq_ws, pooled_ws, T);
   EEG_CHECK_LAUNCH("eeg_pool_tail_bwd");
   const int tot = n_w + (dbias ? T.qmul[0] : 0);
-  k_tail_wgrad<<<(tot + 127) / 128, 128, 0, (cudaStream_t)stream>>>(pooled_ws, dq_ws, dWq, dbias, G, T, n_w);
+  k_tail_wgrad<<<tot, 128, 0, (cudaStream_t)stream>>>(pooled_ws, dq_ws, dWq, dbias, G, T, n_w);
   EEG_CHECK_LAUNCH("eeg_tail_wgrad");
   return 0;
 }

@@ -145,6 +145,11 @@ int eeg_tc_linear_launch(const float* in, const EegLayout* lin, const float* W, 
                          const float* bias, int transB, const float* residual, float* out, const EegLayout* lout, int64_t N,
                          int gate, int gate_off, float act_const, const int32_t* in_ld, const int32_t* k_override, cudaStream_t stream);
 
+// multiplicity-32 streaming path (eeg_lin32.cu): 0 = launched, -1 = shape outside it
+int eeg_lin32_launch(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off, const float* host_scale,
+                     const float* bias, int transB, const float* residual, float* out, const EegLayout* lout, int64_t N,
+                     int gate, int n_scalars, float act_const, const int32_t* in_ld, cudaStream_t stream);
+
 static bool eeg_linear_use_tc() {
   static const char* env = getenv("EEG_LINEAR");  // "cuda": force the CUDA-core GEMM (A/B timing, debugging)
   return !(env && !strcmp(env, "cuda"));
@@ -167,6 +172,12 @@ extern "C" int eeg_gate_linear_fwd(const float* z, const EegLayout* lz, int n_sc
     }
   }
   EEG_REQUIRE(lz->mul[0] == n_scalars + gates, "eeg_gate_linear_fwd: block 0 must hold %d scalars + %d gates", n_scalars, gates);
+  static const char* env = getenv("EEG_LINEAR");
+  if (!(env && !strcmp(env, "tc"))) {
+    const int r32 = eeg_lin32_launch(z, lz, W, host_w_off, host_scale, nullptr, 0, nullptr, out, lout, N, 1, n_scalars, act_const, in_ld,
+                                     (cudaStream_t)stream);
+    if (r32 != -1) return r32;
+  }
   const int rc = eeg_tc_linear_launch(z, lz, W, host_w_off, host_scale, nullptr, 0, nullptr, out, lout, N, 1, n_scalars, act_const,
                                       in_ld, kk, (cudaStream_t)stream);
   if (rc == -1) {
@@ -181,10 +192,18 @@ extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const
                                     float* out, const EegLayout* lout, int64_t N, void* stream) {
   EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_fwd: layout mismatch");
   if (N == 0) return 0;
+  static const char* env32 = getenv("EEG_LINEAR");   // "lin32" / "tc": route the K = 32 shapes to those kernels (A/B timing)
+  if (act == 0 && env32 && !strcmp(env32, "lin32")) {
+    // measured on B200 (N = 30720): 107 / 102 us (product+residual / linear_1) vs 101 / 96 us on the tiled GEMM below, so
+    // the streaming kernel only serves the gate-fused linear_2 (131 us vs 160 us on the tensor-core kernel) by default
+    const int r32 = eeg_lin32_launch(in, lin, W, host_w_off, host_scale, bias, transB, residual, out, lout, N, 0, 0, 0.f, nullptr,
+                                     (cudaStream_t)stream);
+    if (r32 != -1) return r32;
+  }
   if (act == 0 && eeg_linear_use_tc()) {
     // Measured on B200 (N = 30720): the tensor-core kernel wins for the path-stacked interaction.linear (K = 160..320:
-    // 393 us vs 478 us) but not yet for the K = 32 mixes (140-250 us vs 80-100 us: its LDG/STS-staged producers and the
-    // epilogue share one congested memory-instruction queue), so short-K shapes stay on the CUDA-core GEMM.
+    // 393 us vs 478 us) but not for the K = 32 mixes (140-250 us vs 80-100 us on the tiled GEMM: its LDG/STS-staged
+    // producers and the epilogue share one congested memory-instruction queue); those go to eeg_lin32 above.
     bool same_rows = true;
     int max_k = 0;
     for (int b = 0; b < lin->n_blocks; ++b) {
