@@ -148,3 +148,18 @@ def test_full_size_properties_config2(cuda_device):
     with torch.no_grad():
         ref = oracle(sub)["stiffness"]
     assert rel_err(Cs.cpu(), ref) < 1e-4
+
+
+def test_streaming_predictor_matches_direct_calls(cuda_device):
+    """Public end-to-end API (pinned host batches in, pinned host stiffness out, copies overlapped with compute)."""
+    from energy_equiv_lattice_gnn_b200.serve import StreamingPredictor
+    oracle, params = make_pair(0.05)
+    model = cuda_model_from(oracle, params, cuda_device)
+    host = [synthetic_batch(range(4000 + 8 * i, 4000 + 8 * i + 5 + i))[0].pin_memory() for i in range(5)]  # ragged sizes
+    with torch.no_grad():
+        want = [model(b.to(cuda_device))["stiffness"].cpu() for b in host]
+    got = [r.clone() for r in StreamingPredictor(model).run(host)]
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert g.shape == w.shape and torch.equal(g, w)
+    assert list(StreamingPredictor(model).run([])) == []
