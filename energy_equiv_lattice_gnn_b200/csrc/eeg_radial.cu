@@ -2,15 +2,16 @@
 // Replaces `conv_tp_weights` (gnn/blocks.py:538-549,590): Linear(2*nbasis,64) SiLU [Linear(64,64) SiLU]* Linear(64,W).
 //
 // Persistent CTAs (one per SM), each looping over tiles of 128 consecutive CSR edge slots.
-//   warps 0-3 (producer / epilogue, thread = edge for the hidden layers, lane = channel for the output):
+//   warps 0-7 (producer / epilogue, thread = (edge, half of the columns) for the hidden layers, lane = channel for the
+//       output; two warps per SM sub-partition, one alone is latency bound):
 //       first layer on CUDA cores -> hi/lo split (3xTF32, eeg_umma.cuh) -> shared memory in the UMMA K-major layout;
 //       hidden 64x64 layers: tcgen05.mma (M = 128 edges, N = 64), TMEM -> bias + SiLU -> split -> same smem tile;
 //       last layer transposed: D^T[(path,channel), edge] = W[(path,channel), :] . H[edge, :]^T, M = 128 rows =
 //       4 paths x 32 channels, N = 128 edges, so that a TMEM lane is a channel and every st.global of the epilogue
 //       writes one full 128-byte line of the path-major weight tensor  w_t[tile][E][32].
-//   warp 4 (one lane): streams packed weight stages (32 KB, hi+lo) global(L2) -> smem with cp.async.bulk (TMA engine)
+//   warp 8 (one lane): streams packed weight stages (32 KB, hi+lo) global(L2) -> smem with cp.async.bulk (TMA engine)
 //       through a 4-stage mbarrier ring.
-//   warp 5 (one lane): issues tcgen05.mma kind::tf32 (3 MMAs per K-step), fp32 accumulators in TMEM
+//   warp 9 (one lane): issues tcgen05.mma kind::tf32 (3 MMAs per K-step), fp32 accumulators in TMEM
 //       (3 x 128 columns for the output groups + 64 columns for the hidden layers), tcgen05.commit -> mbarriers.
 #include "eeg_common.cuh"
 #include "eeg_umma.cuh"
@@ -29,7 +30,8 @@ constexpr int RM_MAX_HIDDEN = 4;
 constexpr uint32_t RM_TERM_BYTES = RM_EDGES * RM_H * 4;   // 32 KB: one term (hi or lo) of the activation tile
 constexpr uint32_t RM_STAGE_BYTES = 32768;                // hidden: [2][16][64][4] floats; output: [2][8][128][4] floats
 constexpr uint32_t RM_STAGE_FLOATS = RM_STAGE_BYTES / 4;
-constexpr int RM_THREADS = 192;
+constexpr int RM_WORKERS = 256;   // 8 producer / epilogue warps: thread = (edge row, half of the columns)
+constexpr int RM_THREADS = RM_WORKERS + 64;
 
 struct RadialSmem {  // byte offsets into dynamic shared memory
   static constexpr uint32_t HT = 0;                                    // activation tile [2 terms][16 chunks][128 edges][4]
@@ -75,9 +77,9 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
   uint64_t* w_full = bars;                        // [RM_NSTAGE]  loader -> MMA (tx bytes)
   uint64_t* w_empty = w_full + RM_NSTAGE;         // [RM_NSTAGE]  MMA (tcgen05.commit) -> loader
   uint64_t* acc_full = w_empty + RM_NSTAGE;       // [RM_NACC]    MMA -> epilogue
-  uint64_t* acc_empty = acc_full + RM_NACC;       // [RM_NACC]    epilogue (128 threads) -> MMA
+  uint64_t* acc_empty = acc_full + RM_NACC;       // [RM_NACC]    epilogue (256 threads) -> MMA
   uint64_t* hid_full = acc_empty + RM_NACC;       // [1]          MMA -> epilogue (hidden-layer accumulator)
-  uint64_t* h_full = hid_full + 1;                // [1]          producers (128 threads) -> MMA (activation tile ready)
+  uint64_t* h_full = hid_full + 1;                // [1]          producers (256 threads) -> MMA (activation tile ready)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_full + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = (n_ptiles + 3) / 4;               // output groups of 4 path tiles (128 rows)
@@ -86,12 +88,12 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
 
   if (tid == 0) {
     for (int s = 0; s < RM_NSTAGE; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < RM_NACC; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 128); }
+    for (int s = 0; s < RM_NACC; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], RM_WORKERS); }
     mbar_init(hid_full, 1);
-    mbar_init(h_full, 128);
+    mbar_init(h_full, RM_WORKERS);
     mbar_fence_init();
   }
-  if (warp == 5) tmem_alloc(tmem_slot, RM_TMEM_COLS);
+  if (warp == 9) tmem_alloc(tmem_slot, RM_TMEM_COLS);
   float* W0s = reinterpret_cast<float*>(smem + RadialSmem::W0);
   float* b0s = reinterpret_cast<float*>(smem + RadialSmem::B0);
   float* bhs = reinterpret_cast<float*>(smem + RadialSmem::BH);
@@ -106,9 +108,11 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
+  if (warp < 8) {
     // =========================================================== producer / epilogue warps
-    const int r = tid;  // edge row of the tile == TMEM lane for the hidden layers
+    // two warps per SM sub-partition (one alone is latency bound: dependent FMA / MUFU chains, IPC ~0.25)
+    const int r = tid & 127;  // edge row of the tile == TMEM lane for the hidden layers
+    const int hf = tid >> 7;  // which half of the 64 hidden columns / of the 128 edge columns this thread handles
     float4* slot_hi = reinterpret_cast<float4*>(smem + RadialSmem::HT + r * 16);
     float4* slot_lo = reinterpret_cast<float4*>(smem + RadialSmem::HT + RM_TERM_BYTES + r * 16);
     constexpr int CH = RM_EDGES;  // float4 stride between K-chunks
@@ -119,7 +123,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
       slot_hi[c * CH] = hi;
       slot_lo[c * CH] = lo;
     };
-    const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+    const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
     uint32_t hid_it = 0, acc_it = 0;
     for (int64_t tile = blockIdx.x; tile < n_etiles; tile += gridDim.x) {
       const int64_t e0 = tile * RM_EDGES;
@@ -129,7 +133,8 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
 #pragma unroll
         for (int k = 0; k < RM_MAX_IN; ++k) fin[k] = (e < E && k < n_in) ? __ldg(f + e * n_in + k) : 0.f;
 #pragma unroll
-        for (int c = 0; c < RM_H / 4; ++c) {
+        for (int cq = 0; cq < RM_H / 8; ++cq) {
+          const int c = hf * (RM_H / 8) + cq;
           float o[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -154,20 +159,15 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
         mbar_wait(hid_full, hid_it & 1);
         ++hid_it;
         tc_fence_after_sync();
-        uint32_t v0[32], v1[32];
-        tmem_ld_32x32b_x32(tmem_base + lane_base + RM_HID_COL, v0);
-        tmem_ld_32x32b_x32(tmem_base + lane_base + RM_HID_COL + 32, v1);
+        uint32_t v0[32];
+        tmem_ld_32x32b_x32(tmem_base + lane_base + RM_HID_COL + hf * 32, v0);
         tmem_ld_wait();
         tc_fence_before_sync();
-        const float* bl = bhs + l * RM_H;
+        const float* bl = bhs + l * RM_H + hf * 32;
 #pragma unroll
         for (int c = 0; c < 8; ++c)
-          store_split(c, silu_f(__uint_as_float(v0[4 * c]) + bl[4 * c]), silu_f(__uint_as_float(v0[4 * c + 1]) + bl[4 * c + 1]),
+          store_split(hf * 8 + c, silu_f(__uint_as_float(v0[4 * c]) + bl[4 * c]), silu_f(__uint_as_float(v0[4 * c + 1]) + bl[4 * c + 1]),
                       silu_f(__uint_as_float(v0[4 * c + 2]) + bl[4 * c + 2]), silu_f(__uint_as_float(v0[4 * c + 3]) + bl[4 * c + 3]));
-#pragma unroll
-        for (int c = 0; c < 8; ++c)
-          store_split(8 + c, silu_f(__uint_as_float(v1[4 * c]) + bl[32 + 4 * c]), silu_f(__uint_as_float(v1[4 * c + 1]) + bl[32 + 4 * c + 1]),
-                      silu_f(__uint_as_float(v1[4 * c + 2]) + bl[32 + 4 * c + 2]), silu_f(__uint_as_float(v1[4 * c + 3]) + bl[32 + 4 * c + 3]));
         fence_proxy_async_smem();
         mbar_arrive(h_full);
       }
@@ -177,10 +177,10 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
         mbar_wait(&acc_full[a], (acc_it / RM_NACC) & 1);
         ++acc_it;
         tc_fence_after_sync();
-        const int p = 4 * g + warp;
+        const int p = 4 * g + (warp & 3);
         float* dst = w_t + ((int64_t)p * E + e0) * 32 + lane;
 #pragma unroll 1
-        for (int cc = 0; cc < 4; ++cc) {
+        for (int cc = 2 * hf; cc < 2 * hf + 2; ++cc) {
           uint32_t v[32];
           tmem_ld_32x32b_x32(tmem_base + lane_base + (uint32_t)(a * RM_EDGES + cc * 32), v);
           tmem_ld_wait();
@@ -199,7 +199,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
         mbar_arrive(&acc_empty[a]);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     // =========================================================== weight-stage loader (TMA engine bulk copies)
     if (lane == 0) {
       uint32_t it = 0;
@@ -273,7 +273,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  if (warp == 5) tmem_dealloc(tmem_base, RM_TMEM_COLS);
+  if (warp == 9) tmem_dealloc(tmem_base, RM_TMEM_COLS);
 }
 
 }  // namespace
