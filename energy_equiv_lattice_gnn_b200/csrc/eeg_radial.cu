@@ -2,16 +2,16 @@
 // Replaces `conv_tp_weights` (gnn/blocks.py:538-549,590): Linear(2*nbasis,64) SiLU [Linear(64,64) SiLU]* Linear(64,W).
 //
 // Persistent CTAs (one per SM), each looping over tiles of 128 consecutive CSR edge slots.
-//   warps 0-7 (producer / epilogue, thread = (edge, half of the columns) for the hidden layers, lane = channel for the
-//       output; two warps per SM sub-partition, one alone is latency bound):
+//   warps 0-15 (producer / epilogue, thread = (edge, quarter of the columns) for the hidden layers, lane = channel for
+//       the output; four warps per SM sub-partition, one alone is latency bound):
 //       first layer on CUDA cores -> hi/lo split (3xTF32, eeg_umma.cuh) -> shared memory in the UMMA K-major layout;
 //       hidden 64x64 layers: tcgen05.mma (M = 128 edges, N = 64), TMEM -> bias + SiLU -> split -> same smem tile;
 //       last layer transposed: D^T[(path,channel), edge] = W[(path,channel), :] . H[edge, :]^T, M = 128 rows =
 //       4 paths x 32 channels, N = 128 edges, so that a TMEM lane is a channel and every st.global of the epilogue
 //       writes one full 128-byte line of the path-major weight tensor  w_t[tile][E][32].
-//   warp 8 (one lane): streams packed weight stages (32 KB, hi+lo) global(L2) -> smem with cp.async.bulk (TMA engine)
+//   warp 16 (one lane): streams packed weight stages (32 KB, hi+lo) global(L2) -> smem with cp.async.bulk (TMA engine)
 //       through a 4-stage mbarrier ring.
-//   warp 9 (one lane): issues tcgen05.mma kind::tf32 (3 MMAs per K-step), fp32 accumulators in TMEM
+//   warp 17 (one lane): issues tcgen05.mma kind::tf32 (3 MMAs per K-step), fp32 accumulators in TMEM
 //       (3 x 128 columns for the output groups + 64 columns for the hidden layers), tcgen05.commit -> mbarriers.
 #include "eeg_common.cuh"
 #include "eeg_umma.cuh"
@@ -30,7 +30,7 @@ constexpr int RM_MAX_HIDDEN = 4;
 constexpr uint32_t RM_TERM_BYTES = RM_EDGES * RM_H * 4;   // 32 KB: one term (hi or lo) of the activation tile
 constexpr uint32_t RM_STAGE_BYTES = 32768;                // hidden: [2][16][64][4] floats; output: [2][8][128][4] floats
 constexpr uint32_t RM_STAGE_FLOATS = RM_STAGE_BYTES / 4;
-constexpr int RM_WORKERS = 256;   // 8 producer / epilogue warps: thread = (edge row, half of the columns)
+constexpr int RM_WORKERS = 512;   // 16 producer / epilogue warps: thread = (edge row, quarter of the columns)
 constexpr int RM_THREADS = RM_WORKERS + 64;
 
 struct RadialSmem {  // byte offsets into dynamic shared memory
@@ -77,9 +77,9 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
   uint64_t* w_full = bars;                        // [RM_NSTAGE]  loader -> MMA (tx bytes)
   uint64_t* w_empty = w_full + RM_NSTAGE;         // [RM_NSTAGE]  MMA (tcgen05.commit) -> loader
   uint64_t* acc_full = w_empty + RM_NSTAGE;       // [RM_NACC]    MMA -> epilogue
-  uint64_t* acc_empty = acc_full + RM_NACC;       // [RM_NACC]    epilogue (256 threads) -> MMA
+  uint64_t* acc_empty = acc_full + RM_NACC;       // [RM_NACC]    epilogue (512 threads) -> MMA
   uint64_t* hid_full = acc_empty + RM_NACC;       // [1]          MMA -> epilogue (hidden-layer accumulator)
-  uint64_t* h_full = hid_full + 1;                // [1]          producers (256 threads) -> MMA (activation tile ready)
+  uint64_t* h_full = hid_full + 1;                // [1]          producers (512 threads) -> MMA (activation tile ready)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(h_full + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = (n_ptiles + 3) / 4;               // output groups of 4 path tiles (128 rows)
@@ -93,7 +93,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
     mbar_init(h_full, RM_WORKERS);
     mbar_fence_init();
   }
-  if (warp == 9) tmem_alloc(tmem_slot, RM_TMEM_COLS);
+  if (warp == 17) tmem_alloc(tmem_slot, RM_TMEM_COLS);
   float* W0s = reinterpret_cast<float*>(smem + RadialSmem::W0);
   float* b0s = reinterpret_cast<float*>(smem + RadialSmem::B0);
   float* bhs = reinterpret_cast<float*>(smem + RadialSmem::BH);
@@ -108,11 +108,11 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
   tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 8) {
+  if (warp < 16) {
     // =========================================================== producer / epilogue warps
-    // two warps per SM sub-partition (one alone is latency bound: dependent FMA / MUFU chains, IPC ~0.25)
+    // four warps per SM sub-partition (one alone is latency bound: dependent FMA / MUFU chains, IPC ~0.25)
     const int r = tid & 127;  // edge row of the tile == TMEM lane for the hidden layers
-    const int hf = tid >> 7;  // which half of the 64 hidden columns / of the 128 edge columns this thread handles
+    const int hf = tid >> 7;  // which quarter of the 64 hidden columns / of the 128 edge columns this thread handles
     float4* slot_hi = reinterpret_cast<float4*>(smem + RadialSmem::HT + r * 16);
     float4* slot_lo = reinterpret_cast<float4*>(smem + RadialSmem::HT + RM_TERM_BYTES + r * 16);
     constexpr int CH = RM_EDGES;  // float4 stride between K-chunks
@@ -133,8 +133,8 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
 #pragma unroll
         for (int k = 0; k < RM_MAX_IN; ++k) fin[k] = (e < E && k < n_in) ? __ldg(f + e * n_in + k) : 0.f;
 #pragma unroll
-        for (int cq = 0; cq < RM_H / 8; ++cq) {
-          const int c = hf * (RM_H / 8) + cq;
+        for (int cq = 0; cq < RM_H / 16; ++cq) {
+          const int c = hf * (RM_H / 16) + cq;
           float o[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -159,14 +159,14 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
         mbar_wait(hid_full, hid_it & 1);
         ++hid_it;
         tc_fence_after_sync();
-        uint32_t v0[32];
-        tmem_ld_32x32b_x32(tmem_base + lane_base + RM_HID_COL + hf * 32, v0);
+        uint32_t v0[16];
+        tmem_ld_32x32b_x16(tmem_base + lane_base + RM_HID_COL + hf * 16, v0);
         tmem_ld_wait();
         tc_fence_before_sync();
-        const float* bl = bhs + l * RM_H + hf * 32;
+        const float* bl = bhs + l * RM_H + hf * 16;
 #pragma unroll
-        for (int c = 0; c < 8; ++c)
-          store_split(hf * 8 + c, silu_f(__uint_as_float(v0[4 * c]) + bl[4 * c]), silu_f(__uint_as_float(v0[4 * c + 1]) + bl[4 * c + 1]),
+        for (int c = 0; c < 4; ++c)
+          store_split(hf * 4 + c, silu_f(__uint_as_float(v0[4 * c]) + bl[4 * c]), silu_f(__uint_as_float(v0[4 * c + 1]) + bl[4 * c + 1]),
                       silu_f(__uint_as_float(v0[4 * c + 2]) + bl[4 * c + 2]), silu_f(__uint_as_float(v0[4 * c + 3]) + bl[4 * c + 3]));
         fence_proxy_async_smem();
         mbar_arrive(h_full);
@@ -180,7 +180,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
         const int p = 4 * g + (warp & 3);
         float* dst = w_t + ((int64_t)p * E + e0) * 32 + lane;
 #pragma unroll 1
-        for (int cc = 2 * hf; cc < 2 * hf + 2; ++cc) {
+        for (int cc = hf; cc < hf + 1; ++cc) {
           uint32_t v[32];
           tmem_ld_32x32b_x32(tmem_base + lane_base + (uint32_t)(a * RM_EDGES + cc * 32), v);
           tmem_ld_wait();
@@ -199,7 +199,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
         mbar_arrive(&acc_empty[a]);
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == 16) {
     // =========================================================== weight-stage loader (TMA engine bulk copies)
     if (lane == 0) {
       uint32_t it = 0;
@@ -273,7 +273,7 @@ k_radial_mlp(const float* __restrict__ f, int n_in, const float* __restrict__ W0
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  if (warp == 9) tmem_dealloc(tmem_base, RM_TMEM_COLS);
+  if (warp == 17) tmem_dealloc(tmem_base, RM_TMEM_COLS);
 }
 
 }  // namespace
