@@ -16,7 +16,7 @@
 
 namespace {
 
-constexpr int WARPS = 4, NPW = 16;
+constexpr int WARPS = 4, NPW = 4;   // small row ranges: the kernel is bound by global-load latency, it needs many warps in flight
 
 template <int LIN, int LMAX>
 struct TpB;
