@@ -8,6 +8,7 @@ parameter / buffer names as the reference module tree so a re
 from __future__ import annotations
 
 import math
+import os
 from argparse import Namespace
 from typing import Dict, List
 
@@ -234,6 +235,7 @@ class EnergyEquivGNN(torch.nn.Module):
         sC = 1.0 / math.sqrt(C)
         if save is not None:
             save.update(row_ptr=row_ptr, perm=perm, gp=gp, Y=Y, f=f, snd=snd, h_in=[], hup=[], acts=[], w=[], M=[], msg=[], B=[])
+        o_chain = None
         for i, layer in enumerate(head.layers):
             inter, prod = layer.interaction, layer.product
             lay_in = self._lay_h0 if i == 0 else self._lay_h
@@ -256,8 +258,21 @@ class EnergyEquivGNN(torch.nn.Module):
                                   self._lay_h, N, bias=inter.linear.bias.detach())
             nv.set_tag(f'L{i}.sym_contract')
             B = nv.sym_contract(lmax, self.correlation, C, msg, self._sc_table(i), N)
+            poff = [b * C * C for b in range(lmax + 1)]
+            if save is None and i == len(head.layers) - 1 and os.environ.get("EEG_READOUT_CHAIN", "1") != "0":
+                # inference, last layer: product.linear (+ residual) -> linear_1 -> Gate -> linear_2 chained in one pass;
+                # h and z are never written (None when the shape is outside that kernel: the unfused calls below run)
+                ro = head.nonlin_readout
+                nv.set_tag('readout.chain')
+                o_chain = nv.readout_chain(B, h if i > 0 else None, self._lay_h, prod.linear.weight.detach(), poff, [sC] * (lmax + 1),
+                                           ro.linear_1.weight.detach(), [0] + [C * (C + C * lmax) + b * C * C for b in range(lmax)],
+                                           [sC] * (lmax + 1), ro.linear_2.weight.detach(),
+                                           np.concatenate(([0], np.cumsum([C * m for m in self.rmul])))[:-1].tolist(),
+                                           [sC] * (lmax + 1), NORM2MOM_SILU, self._lay_o, N)
+                if o_chain is not None:
+                    break
             nv.set_tag(f'L{i}.product_linear')
-            h_new = nv.block_linear(B, self._lay_h, prod.linear.weight.detach(), [b * C * C for b in range(lmax + 1)],
+            h_new = nv.block_linear(B, self._lay_h, prod.linear.weight.detach(), poff,
                                     [sC] * (lmax + 1), self._lay_h, N, residual=h if i > 0 else None)
             if save is not None:
                 save["h_in"].append(h); save["hup"].append(hup); save["acts"].append(acts); save["w"].append(w)
@@ -266,11 +281,13 @@ class EnergyEquivGNN(torch.nn.Module):
         ro = head.nonlin_readout
         n_gates = C * lmax
         w1off = [0] + [C * (C + n_gates) + b * C * C for b in range(lmax)]
-        nv.set_tag('readout.linear_1')
-        z = nv.block_linear(h, self._lay_h, ro.linear_1.weight.detach(), w1off, [sC] * (lmax + 1), self._lay_z, N)
         w2off = np.concatenate(([0], np.cumsum([C * m for m in self.rmul])))[:-1].tolist()
-        g = o = None
-        if save is None:  # inference: Gate applied while linear_2's operand rows are staged (no gated tensor in HBM)
+        g = z = None
+        o = o_chain
+        if o is None:
+            nv.set_tag('readout.linear_1')
+            z = nv.block_linear(h, self._lay_h, ro.linear_1.weight.detach(), w1off, [sC] * (lmax + 1), self._lay_z, N)
+        if o is None and save is None:  # inference: Gate applied while linear_2's operand rows are staged (no gated tensor in HBM)
             nv.set_tag('readout.gate_linear_2')
             o = nv.gate_linear(z, self._lay_z, C, NORM2MOM_SILU, ro.linear_2.weight.detach(), w2off, [sC] * (lmax + 1), self._lay_o, N)
         if o is None:

@@ -17,7 +17,7 @@ EEG_MAX_L = 8
 
 SYMBOLS = [
     "eeg_last_error", "eeg_abi_version", "eeg_csr_workspace_bytes", "eeg_csr_build", "eeg_graph_ptr",
-    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_gate_linear_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
+    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_gate_linear_fwd", "eeg_readout_chain_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
     "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd", "eeg_radial_image_floats", "eeg_radial_pack", "eeg_radial_mlp_fwd",
     # explicit backward ops + optimizer
     "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
@@ -68,7 +68,7 @@ def lib() -> C.CDLL:
 KERNELS_PER_CALL = {"eeg_csr_build": 6, "eeg_graph_ptr": 1, "eeg_node_embed_fwd": 1, "eeg_edge_featurize": 1,
                     "eeg_block_linear_fwd": 1, "eeg_gate_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
                     "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1,
-                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1, "eeg_pool_tail_bwd": 2}
+                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1, "eeg_pool_tail_bwd": 2, "eeg_readout_chain_fwd": 2}
 launch_count = 0
 _events = None  # list of (name, tag, start_event, end_event) while profiling
 _tag = ""
@@ -203,6 +203,25 @@ def gate_linear(z, lz: EegLayout, n_scalars: int, act_const: float, W, w_off: Se
     _begin("eeg_gate_linear_fwd")
     _check(lib().eeg_gate_linear_fwd(_p(z, f32), C.byref(lz), C.c_int(n_scalars), C.c_float(act_const), _p(W, f32), woff, sc,
                                      _p(out, f32), C.byref(lout), C.c_int64(n_rows), _stream()), "eeg_gate_linear_fwd")
+    return out
+
+
+def readout_chain(B, residual, lh: EegLayout, Wp, wp_off, sp, W1, w1_off, s1, W2, w2_off, s2, act_const: float, lout: EegLayout,
+                  n_rows: int):
+    """Inference tail product.linear(+residual) -> linear_1 -> Gate -> linear_2 in one pass (multiplicity-32 models).
+    Returns o [N, lout.stride], or None when the shape is outside the fused kernel."""
+    nb = lh.n_blocks
+    if any(lh.mul[b] != 32 for b in range(nb)) or any(not (1 <= lout.mul[b] <= 32) for b in range(nb)) or nb > 5:
+        return None
+    out = torch.empty(n_rows, lout.stride, dtype=f32, device=B.device)
+    gates = torch.empty(n_rows, max(1, 32 * (nb - 1)), dtype=f32, device=B.device)
+    arr_i = lambda v: (C.c_int64 * EEG_MAX_L)(*list(v) + [0] * (EEG_MAX_L - nb))  # noqa: E731
+    arr_f = lambda v: (C.c_float * EEG_MAX_L)(*list(v) + [0.0] * (EEG_MAX_L - nb))  # noqa: E731
+    _begin("eeg_readout_chain_fwd")
+    _check(lib().eeg_readout_chain_fwd(_p(B, f32), _p(residual, f32) if residual is not None else None, C.byref(lh), _p(Wp, f32),
+                                       arr_i(wp_off), arr_f(sp), _p(W1, f32), arr_i(w1_off), arr_f(s1), _p(W2, f32), arr_i(w2_off),
+                                       arr_f(s2), C.c_float(act_const), _p(gates), _p(out), C.byref(lout), C.c_int64(n_rows), _stream()),
+           "eeg_readout_chain_fwd")
     return out
 
 

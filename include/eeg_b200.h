@@ -158,6 +158,16 @@ int eeg_sc_coef_grad(int lmax, int nu, int C, const float* x, const float* dout,
 int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,
                             float* dT, int C, float* dW, void* stream);
 
+/* ---- fused inference tail for multiplicity-32 models: product.linear (+ residual) -> readout linear_1 -> Gate -> linear_2
+ * (gnn/blocks.py:471-476,488-490, gnn/model.py:95-96, gnn/blocks.py:250-283) in one streaming pass per irrep block; only
+ * out [N, lout] and the gate activations (scratch `gates` [N, 32 (n_blocks - 1)]) are written.  lh: layout of B / residual
+ * (every block multiplicity 32, rows 2l+1, l <= 4); residual may be NULL.  Weight offsets / scales per block as in
+ * eeg_block_linear_fwd; W1's 0e block is [32][32 + 32 (n_blocks - 1)] (scalars first, then the gates of l = 1, 2, ...). */
+int eeg_readout_chain_fwd(const float* B, const float* residual, const EegLayout* lh, const float* Wp, const int64_t* host_wp_off,
+                          const float* host_sp, const float* W1, const int64_t* host_w1_off, const float* host_s1, const float* W2,
+                          const int64_t* host_w2_off, const float* host_s2, float act_const, float* gates, float* out,
+                          const EegLayout* lout, int64_t N, void* stream);
+
 /* ---- optimizer step (scripts/train_utils.py:38-44 AdamW(amsgrad), scripts/train_main.py:91 gradient_clip_val) on flat
  * fp32 buffers.  eeg_sumsq: out[0] += sum x^2.  eeg_adamw_step: g' = grad_scale * g clipped to max_norm by the global norm
  * sqrt(gnorm_sq[0]) * grad_scale (gnorm_sq NULL or max_norm <= 0: no clipping); vmax NULL: plain AdamW. step counts from 1. */
