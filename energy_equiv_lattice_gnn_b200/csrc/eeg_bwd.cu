@@ -88,14 +88,24 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
 }
 
 // ------------------------------------------------------------------------------------------------ column sums
-__global__ void k_colsum(const float* __restrict__ x, int64_t R, int ld, int cols, const float* __restrict__ a, float* __restrict__ out,
-                         int rows_per_cta) {
-  const int c = blockIdx.y * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+// block = 32 columns x 8 row lanes; a CTA sums rows_per_cta rows (fixed order inside the CTA), one atomicAdd per column
+__global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ x, int64_t R, int ld, int cols, const float* __restrict__ a,
+                                                float* __restrict__ out, int rows_per_cta) {
+  __shared__ float part[8][33];
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = blockIdx.y * 32 + cl;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta, r1 = r0 + rows_per_cta < R ? r0 + rows_per_cta : R;
   float s = 0.f;
-  for (int64_t r = r0; r < r1; ++r) s = fmaf(a ? __ldg(a + r) : 1.0f, __ldg(x + r * ld + c), s);
-  atomicAdd(out + c, s);
+  if (c < cols)
+    for (int64_t r = r0 + rl; r < r1; r += 8) s = fmaf(a ? __ldg(a + r) : 1.0f, __ldg(x + r * ld + c), s);
+  part[rl][cl] = s;
+  __syncthreads();
+  if (rl == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) t += part[q][cl];
+    atomicAdd(out + c, t);
+  }
 }
 
 __global__ void k_silu_fwd(const float* __restrict__ a, float* __restrict__ s, int64_t n) {
@@ -342,9 +352,9 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
 
 extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream) {
   if (R == 0 || cols == 0) return 0;
-  const int rows_per_cta = 1024;
-  dim3 grid((unsigned)((R + rows_per_cta - 1) / rows_per_cta), (unsigned)((cols + 127) / 128));
-  k_colsum<<<grid, 128, 0, (cudaStream_t)stream>>>(x, R, ld, cols, row_scale, out, rows_per_cta);
+  const int rows_per_cta = 256;
+  dim3 grid((unsigned)((R + rows_per_cta - 1) / rows_per_cta), (unsigned)((cols + 31) / 32));
+  k_colsum<<<grid, 256, 0, (cudaStream_t)stream>>>(x, R, ld, cols, row_scale, out, rows_per_cta);
   EEG_CHECK_LAUNCH("eeg_colsum");
   return 0;
 }
