@@ -150,6 +150,11 @@ int eeg_lin32_launch(const float* in, const EegLayout* lin, const float* W, cons
                      const float* bias, int transB, const float* residual, float* out, const EegLayout* lout, int64_t N,
                      int gate, int n_scalars, float act_const, const int32_t* in_ld, cudaStream_t stream);
 
+// multiplicity-32 warp-MMA path (eeg_lin32mma.cu): 0 = launched, -1 = shape outside it
+int eeg_lin32_mma_launch(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off, const float* host_scale,
+                         const float* bias, int transB, const float* residual, float* out, const EegLayout* lout, int64_t N,
+                         cudaStream_t stream);
+
 static bool eeg_linear_use_tc() {
   static const char* env = getenv("EEG_LINEAR");  // "cuda": force the CUDA-core GEMM (A/B timing, debugging)
   return !(env && !strcmp(env, "cuda"));
@@ -192,7 +197,12 @@ extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const
                                     float* out, const EegLayout* lout, int64_t N, void* stream) {
   EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_fwd: layout mismatch");
   if (N == 0) return 0;
-  static const char* env32 = getenv("EEG_LINEAR");   // "lin32" / "tc": route the K = 32 shapes to those kernels (A/B timing)
+  static const char* env32 = getenv("EEG_LINEAR");   // "lin32" / "tc" / "cuda": route the K = 32 shapes to those kernels (A/B timing)
+  if (act == 0 && env32 == nullptr) {
+    // multiplicity-32 inputs: node-major warp-level tensor-core kernel (eeg_lin32mma.cu)
+    const int rm = eeg_lin32_mma_launch(in, lin, W, host_w_off, host_scale, bias, transB, residual, out, lout, N, (cudaStream_t)stream);
+    if (rm != -1) return rm;
+  }
   if (act == 0 && env32 && !strcmp(env32, "lin32")) {
     // measured on B200 (N = 30720): 107 / 102 us (product+residual / linear_1) vs 101 / 96 us on the tiled GEMM below, so
     // the streaming kernel only serves the gate-fused linear_2 (131 us vs 160 us on the tensor-core kernel) by default
