@@ -7,6 +7,8 @@
 // eeg_lin32.cu), each stage's result goes back to the warp's shared-memory slot as the broadcast operand of the next one,
 // and only o [N, D, mul_out] (plus the [N, 32 (L-1)] gate activations, written by the 0e pass) reaches HBM: h and z are
 // never materialised.  Two launches: the 0e block first (it produces the gates), then the gated blocks.
+#include <stdlib.h>
+#include <string.h>
 #include "eeg_common.cuh"
 
 namespace {
@@ -235,6 +237,12 @@ __global__ void __launch_bounds__(RC_WARPS * 32, 2) k_readout_chain(const float*
 
 }  // namespace
 
+// warp-level tensor-core version (eeg_readout_mma.cu): 0 = launched, -1 = shape outside it
+int eeg_readout_chain_mma_launch(const float* B, const float* residual, const EegLayout* lh, const float* Wp,
+                                 const int64_t* host_wp_off, const float* host_sp, const float* W1, const int64_t* host_w1_off,
+                                 const float* host_s1, const float* W2, const int64_t* host_w2_off, const float* host_s2,
+                                 float act_const, float* gates, float* out, const EegLayout* lout, int64_t N, cudaStream_t stream);
+
 extern "C" int eeg_readout_chain_fwd(const float* B, const float* residual, const EegLayout* lh, const float* Wp,
                                      const int64_t* host_wp_off, const float* host_sp, const float* W1, const int64_t* host_w1_off,
                                      const float* host_s1, const float* W2, const int64_t* host_w2_off, const float* host_s2,
@@ -242,6 +250,14 @@ extern "C" int eeg_readout_chain_fwd(const float* B, const float* residual, cons
   EEG_REQUIRE(lh && lout && lh->n_blocks == lout->n_blocks && lh->n_blocks >= 1 && lh->n_blocks <= EEG_MAX_L,
               "eeg_readout_chain_fwd: layout mismatch");
   if (N == 0) return 0;
+  {
+    static const char* env = getenv("EEG_CHAIN");   // "cuda": force the CUDA-core chain below (A/B timing)
+    if (!(env && !strcmp(env, "cuda"))) {
+      const int rm = eeg_readout_chain_mma_launch(B, residual, lh, Wp, host_wp_off, host_sp, W1, host_w1_off, host_s1, W2, host_w2_off,
+                                                  host_s2, act_const, gates, out, lout, N, (cudaStream_t)stream);
+      if (rm != -1) return rm;
+    }
+  }
   RcParams P;
   P.n_blocks = lh->n_blocks;
   P.in_stride = lh->stride;
