@@ -5,11 +5,11 @@
 // quad shuffles (no shared memory round trip); the three weight matrices of every block sit in shared memory as hi/lo B
 // fragments.  Pass 0 = the 0e block (scalars + the gate activations, written to `gates`), pass 1 = the gated blocks.
 #include "eeg_common.cuh"
+#include "eeg_mma.cuh"
 
 namespace {
 
 constexpr int CM_WARPS = 16, CM_NB = 32, CM_MAXB = 5;
-constexpr int CM_FRAG = 4 * 32;   // floats per (8-column tile, k-step): [b0 hi | b0 lo | b1 hi | b1 lo][lane]
 
 struct CmBlock {
   int rows, nout, in_off, out_off, blk;
@@ -25,48 +25,6 @@ struct CmParams {
   float act_const;
   unsigned char warp_group[CM_WARPS], warp_rank[CM_WARPS], group_warps[CM_MAXB];
 };
-
-__device__ __forceinline__ uint32_t cm_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return r;
-}
-__device__ __forceinline__ void cm_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-// acc[j] += A (k-step s, fp32 values split hi/lo) x W fragments (tile j, k-step s) for j < NT
-template <int NT>
-__device__ __forceinline__ void cm_kstep(float (&acc)[4][4], const float (&av)[4], const float* frag, int s) {
-  uint32_t ah[4], al[4];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    ah[q] = cm_tf32(av[q]);
-    al[q] = __float_as_uint(av[q] - __uint_as_float(ah[q]));
-  }
-#pragma unroll
-  for (int j = 0; j < NT; ++j) {
-    const float* f = frag + (j * 4 + s) * CM_FRAG;
-    const uint32_t b0h = __float_as_uint(f[0]), b0l = __float_as_uint(f[32]), b1h = __float_as_uint(f[64]), b1l = __float_as_uint(f[96]);
-    cm_mma(acc[j], al, b0h, b1h);
-    cm_mma(acc[j], ah, b0l, b1l);
-    cm_mma(acc[j], ah, b0h, b1h);
-  }
-}
-// accumulator fragment (columns 8 s .. 8 s + 7 of a 16-row tile) -> A fragment of k-step s
-__device__ __forceinline__ void cm_c2a(const float (&c)[4], float (&a)[4], int lane) {
-  const int t = lane & 3, src1 = (lane & ~3) | (t >> 1), src2 = src1 + 2;
-  const bool odd = t & 1;
-  const float p0 = __shfl_sync(0xffffffffu, c[0], src1), p1 = __shfl_sync(0xffffffffu, c[1], src1);
-  const float p2 = __shfl_sync(0xffffffffu, c[2], src1), p3 = __shfl_sync(0xffffffffu, c[3], src1);
-  const float q0 = __shfl_sync(0xffffffffu, c[0], src2), q1 = __shfl_sync(0xffffffffu, c[1], src2);
-  const float q2 = __shfl_sync(0xffffffffu, c[2], src2), q3 = __shfl_sync(0xffffffffu, c[3], src2);
-  a[0] = odd ? p1 : p0;   // (row g,     col t)
-  a[1] = odd ? p3 : p2;   // (row g + 8, col t)
-  a[2] = odd ? q1 : q0;   // (row g,     col t + 4)
-  a[3] = odd ? q3 : q2;   // (row g + 8, col t + 4)
-}
 
 template <int PASS>
 __global__ void __launch_bounds__(CM_WARPS * 32, 1) k_chain_mma(const float* __restrict__ Bx, const float* __restrict__ res,

@@ -235,13 +235,16 @@ class EnergyEquivGNN(torch.nn.Module):
         sC = 1.0 / math.sqrt(C)
         if save is not None:
             save.update(row_ptr=row_ptr, perm=perm, gp=gp, Y=Y, f=f, snd=snd, h_in=[], hup=[], acts=[], w=[], M=[], msg=[], B=[])
-        o_chain = None
+        o_chain = hup_next = None
         for i, layer in enumerate(head.layers):
             inter, prod = layer.interaction, layer.product
             lay_in = self._lay_h0 if i == 0 else self._lay_h
             nblk = lay_in.n_blocks
-            nv.set_tag(f'L{i}.linear_up')
-            hup = nv.block_linear(h, lay_in, inter.linear_up.weight.detach(), [b * C * C for b in range(nblk)], [sC] * nblk, lay_in, N)
+            if hup_next is not None:   # produced together with the previous layer's product.linear
+                hup, hup_next = hup_next, None
+            else:
+                nv.set_tag(f'L{i}.linear_up')
+                hup = nv.block_linear(h, lay_in, inter.linear_up.weight.detach(), [b * C * C for b in range(nblk)], [sC] * nblk, lay_in, N)
             # radial MLP (gnn/blocks.py:538-549,590): fused, last layers on tcgen05; output path-major w_t[P*C/32, E, 32]
             lins = [m for m in inter.conv_tp_weights if isinstance(m, torch.nn.Linear)]
             nv.set_tag(f'L{i}.radial_mlp')
@@ -271,9 +274,18 @@ class EnergyEquivGNN(torch.nn.Module):
                                            [sC] * (lmax + 1), NORM2MOM_SILU, self._lay_o, N)
                 if o_chain is not None:
                     break
-            nv.set_tag(f'L{i}.product_linear')
-            h_new = nv.block_linear(B, self._lay_h, prod.linear.weight.detach(), poff,
-                                    [sC] * (lmax + 1), self._lay_h, N, residual=h if i > 0 else None)
+            h_new = None
+            if save is None and i + 1 < len(head.layers) and os.environ.get("EEG_LINEAR_PAIR", "1") != "0":
+                # inference: product.linear of this layer and linear_up of the next one chained in one pass
+                nv.set_tag(f'L{i}.product_linear+L{i + 1}.linear_up')
+                pair = nv.linear_pair(B, h if i > 0 else None, self._lay_h, prod.linear.weight.detach(), poff, [sC] * (lmax + 1),
+                                      head.layers[i + 1].interaction.linear_up.weight.detach(), poff, [sC] * (lmax + 1), N)
+                if pair is not None:
+                    h_new, hup_next = pair
+            if h_new is None:
+                nv.set_tag(f'L{i}.product_linear')
+                h_new = nv.block_linear(B, self._lay_h, prod.linear.weight.detach(), poff,
+                                        [sC] * (lmax + 1), self._lay_h, N, residual=h if i > 0 else None)
             if save is not None:
                 save["h_in"].append(h); save["hup"].append(hup); save["acts"].append(acts); save["w"].append(w)
                 save["M"].append(M); save["msg"].append(msg); save["B"].append(B)

@@ -17,7 +17,7 @@ EEG_MAX_L = 8
 
 SYMBOLS = [
     "eeg_last_error", "eeg_abi_version", "eeg_csr_workspace_bytes", "eeg_csr_build", "eeg_graph_ptr",
-    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_gate_linear_fwd", "eeg_readout_chain_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
+    "eeg_edge_featurize", "eeg_block_linear_fwd", "eeg_gate_linear_fwd", "eeg_readout_chain_fwd", "eeg_linear_pair_fwd", "eeg_tp_scatter_fwd", "eeg_sc_coefficients", "eeg_sym_contract_fwd",
     "eeg_gate_fwd", "eeg_pool_tail_fwd", "eeg_node_embed_fwd", "eeg_radial_image_floats", "eeg_radial_pack", "eeg_radial_mlp_fwd",
     # explicit backward ops + optimizer
     "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
@@ -68,7 +68,7 @@ def lib() -> C.CDLL:
 KERNELS_PER_CALL = {"eeg_csr_build": 6, "eeg_graph_ptr": 1, "eeg_node_embed_fwd": 1, "eeg_edge_featurize": 1,
                     "eeg_block_linear_fwd": 1, "eeg_gate_linear_fwd": 1, "eeg_tp_scatter_fwd": 1, "eeg_sc_coefficients": 1,
                     "eeg_sym_contract_fwd": 1, "eeg_gate_fwd": 1, "eeg_pool_tail_fwd": 1,
-                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1, "eeg_pool_tail_bwd": 2, "eeg_readout_chain_fwd": 2}
+                    "eeg_radial_pack": 1, "eeg_radial_mlp_fwd": 1, "eeg_pool_tail_bwd": 2, "eeg_readout_chain_fwd": 2, "eeg_linear_pair_fwd": 1}
 launch_count = 0
 _events = None  # list of (name, tag, start_event, end_event) while profiling
 _tag = ""
@@ -204,6 +204,21 @@ def gate_linear(z, lz: EegLayout, n_scalars: int, act_const: float, W, w_off: Se
     _check(lib().eeg_gate_linear_fwd(_p(z, f32), C.byref(lz), C.c_int(n_scalars), C.c_float(act_const), _p(W, f32), woff, sc,
                                      _p(out, f32), C.byref(lout), C.c_int64(n_rows), _stream()), "eeg_gate_linear_fwd")
     return out
+
+
+def linear_pair(x, residual, lh: EegLayout, Wa, wa_off, sa, Wb, wb_off, sb, n_rows: int):
+    """y1 = Wa x (+ residual), y2 = Wb y1 in one pass (multiplicity-32 blocks).  Returns (y1, y2) or None if unsupported."""
+    nb = lh.n_blocks
+    if any(lh.mul[b] != 32 for b in range(nb)) or nb > 5:
+        return None
+    y1, y2 = torch.empty_like(x), torch.empty_like(x)
+    arr_i = lambda v: (C.c_int64 * EEG_MAX_L)(*list(v) + [0] * (EEG_MAX_L - nb))  # noqa: E731
+    arr_f = lambda v: (C.c_float * EEG_MAX_L)(*list(v) + [0.0] * (EEG_MAX_L - nb))  # noqa: E731
+    _begin("eeg_linear_pair_fwd")
+    _check(lib().eeg_linear_pair_fwd(_p(x, f32), _p(residual, f32) if residual is not None else None, C.byref(lh), _p(Wa, f32),
+                                     arr_i(wa_off), arr_f(sa), _p(Wb, f32), arr_i(wb_off), arr_f(sb), _p(y1), _p(y2),
+                                     C.c_int64(n_rows), _stream()), "eeg_linear_pair_fwd")
+    return y1, y2
 
 
 def readout_chain(B, residual, lh: EegLayout, Wp, wp_off, sp, W1, w1_off, s1, W2, w2_off, s2, act_const: float, lout: EegLayout,

@@ -158,6 +158,13 @@ int eeg_sc_coef_grad(int lmax, int nu, int C, const float* x, const float* dout,
 int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,
                             float* dT, int C, float* dW, void* stream);
 
+/* ---- two chained multiplicity-32 per-irrep mixes in one pass (inference): y1 = Wa x (+ residual) = product.linear of layer i
+ * (gnn/blocks.py:471-476,488-490, gnn/model.py:95-96), y2 = Wb y1 = linear_up of layer i+1 (gnn/blocks.py:516-521,589).
+ * x, residual (may be NULL), y1, y2 share the layout lh (every block multiplicity 32); weights [32][32] per block. */
+int eeg_linear_pair_fwd(const float* x, const float* residual, const EegLayout* lh, const float* Wa, const int64_t* host_wa_off,
+                        const float* host_sa, const float* Wb, const int64_t* host_wb_off, const float* host_sb, float* y1,
+                        float* y2, int64_t N, void* stream);
+
 /* ---- fused inference tail for multiplicity-32 models: product.linear (+ residual) -> readout linear_1 -> Gate -> linear_2
  * (gnn/blocks.py:471-476,488-490, gnn/model.py:95-96, gnn/blocks.py:250-283) in one streaming pass per irrep block; only
  * out [N, lout] and the gate activations (scratch `gates` [N, 32 (n_blocks - 1)]) are written.  lh: layout of B / residual
