@@ -120,6 +120,20 @@ def algorithmic_model(model, n_nodes: int, n_edges: int):
     return out
 
 
+def ncu_traffic(tag, n_nodes, n_edges):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel behind `tag`, from the committed
+    `ncu --set full` capture (profiles/ncu_traffic.json); None when no capture exists for this workload size."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")
+    try:
+        with open(path) as f:
+            ent = json.load(f).get(tag)
+    except (OSError, ValueError):
+        return None, None
+    if not ent or ent.get("n_nodes") != n_nodes or ent.get("n_edges") != n_edges:
+        return None, None
+    return ent["dram_bytes_read"] + ent["dram_bytes_write"], ent.get("source")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -281,8 +295,9 @@ def main():
     top = max((k for k in kern if k in alg), key=lambda k: kern[k])
     top_ms = kern[top]
     achieved = alg[top]["bytes"] / (top_ms * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(top, n_nodes, n_edges)
     roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "ms_per_launch": top_ms, "share_of_step": top_ms / step_sum,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "ms_per_launch": top_ms, "share_of_step": top_ms / step_sum,
                 "algorithmic_bytes_per_launch": alg[top]["bytes"], "algorithmic_flops_per_launch": alg[top]["flops"],
                 "fp32_tflops_achieved": alg[top]["flops"] / (top_ms * 1e-3) / 1e12,
                 "fp32_tflops_peak_measured": 68.3, "fp32_peak_source": "tools/micro/ffma2_rate.cu on B200: 2.17 clk per FFMA2 per SMSP at 1.95 GHz",

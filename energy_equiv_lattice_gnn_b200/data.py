@@ -200,3 +200,67 @@ def synthetic_batch(seeds: Sequence[int], n_nodes: int = 30, with_target: bool =
     data = [synthetic_lattice(s, n_nodes, with_target=with_target) for s in seeds]
     rmax = max(float(d.edge_attr.max()) for d in data)
     return collate(data), rmax
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# RotateLat on a collated device batch (scripts/train_utils.py:114-146; SURVEY.md section 8(f) rank 1)
+# ------------------------------------------------------------------------------------------------------------------
+def rand_rotations(n: int, generator: Optional[torch.Generator] = None, dtype=torch.float32) -> torch.Tensor:
+    """[n,3,3] random proper rotations, the distribution of e3nn `o3.rand_matrix()` (train_utils.py:121): alpha, gamma
+    uniform on [0, 2pi), cos(beta) uniform on [-1, 1], R = Ry(alpha) Rx(beta) Ry(gamma)."""
+    u = torch.rand(3, n, generator=generator, dtype=torch.float64)
+    alpha, gamma = 2 * math.pi * u[0], 2 * math.pi * u[2]
+    beta = torch.acos(2 * u[1] - 1)
+
+    def ry(a):
+        c, s, o, z = a.cos(), a.sin(), torch.ones_like(a), torch.zeros_like(a)
+        return torch.stack([c, z, s, z, o, z, -s, z, c], -1).reshape(-1, 3, 3)
+
+    def rx(a):
+        c, s, o, z = a.cos(), a.sin(), torch.ones_like(a), torch.zeros_like(a)
+        return torch.stack([o, z, z, z, c, -s, z, s, c], -1).reshape(-1, 3, 3)
+
+    return (ry(alpha) @ rx(beta) @ ry(gamma)).to(dtype)
+
+
+class RotateLat:
+    """Batched, on-device counterpart of the reference's per-lattice `RotateLat` transform (scripts/train_utils.py:114-146).
+
+    `__call__(batch, Q=None)` takes a collated CUDA `Batch` whose targets are still Cartesian rank-4 tensors
+    (`stiffness`, and optionally `compliance`, `[G,3,3,3,3]`, as `GLAMM_Dataset.process_one` stores them for
+    'cartesian_4', gnn/datasets.py:256-269) and returns a new `Batch` with rotated `positions` / `shifts` and Mandel
+    `[G,6,6]` targets.  `Q` is `[G,3,3]` (one rotation per lattice, drawn like `o3.rand_matrix()` when omitted);
+    `rotate=False` only converts the targets, and then `Q` must be None, as in the reference (:126-127).
+    CUDA only: the kernels live in libeeg_b200 (`eeg_rotate_vec3`, `eeg_rotate_cart4_to_mandel`)."""
+
+    def __init__(self, rotate: bool = True, generator: Optional[torch.Generator] = None):
+        self.rotate = rotate
+        self.generator = generator
+
+    def __call__(self, batch: Batch, Q: Optional[torch.Tensor] = None) -> Batch:
+        from . import native
+        G = int(batch.num_graphs)
+        dev = batch.positions.device
+        out = Batch(**batch.__dict__)
+        if self.rotate:
+            if Q is None:
+                Q = rand_rotations(G, self.generator)
+            Q = Q.to(device=dev, dtype=torch.float32).contiguous()
+            if Q.shape != (G, 3, 3):
+                raise ValueError(f"Q must be [{G},3,3], got {tuple(Q.shape)}")
+            out.positions = torch.empty_like(batch.positions)
+            out.shifts = torch.empty_like(batch.shifts)
+            native.rotate_vec3(Q, batch.batch, None, batch.positions.contiguous(), out.positions)
+            native.rotate_vec3(Q, batch.batch, batch.edge_index[0].contiguous(), batch.shifts.contiguous(), out.shifts)
+        else:
+            assert Q is None, "Q should be None if instance initialized with rotate=False"
+        for key in ("stiffness", "compliance"):
+            t = getattr(batch, key, None)
+            if t is None:
+                continue
+            if tuple(t.shape[1:]) != (3, 3, 3, 3):
+                raise ValueError(f"batch.{key} must be Cartesian rank-4 [G,3,3,3,3], got {tuple(t.shape)}")
+            m = torch.empty(G, 6, 6, dtype=torch.float32, device=dev)
+            native.rotate_cart4_to_mandel(Q if self.rotate else None, t.to(torch.float32).contiguous(), m)
+            setattr(out, key, m)
+        return out

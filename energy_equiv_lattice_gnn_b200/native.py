@@ -22,7 +22,7 @@ SYMBOLS = [
     # explicit backward ops + optimizer
     "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
-    "eeg_sumsq", "eeg_adamw_step",
+    "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics",
 ]
 
 
@@ -429,3 +429,25 @@ def adamw_step(p, g, m, v, vmax, lr, beta1, beta2, eps, weight_decay, step, gnor
     _check(lib().eeg_adamw_step(_p(p, f32), _p(g, f32), _p(m, f32), _p(v, f32), _p(vmax, f32), C.c_int64(p.numel()), C.c_float(lr), C.c_float(beta1),
                                 C.c_float(beta2), C.c_float(eps), C.c_float(weight_decay), C.c_int(step), _p(gnorm_sq, f32), C.c_float(max_norm),
                                 C.c_float(grad_scale), _stream()), "eeg_adamw_step")
+
+
+def rotate_vec3(Q, graph_of, via, x, out):
+    """out[i] = Q[graph_of[via[i] if via is not None else i]] @ x[i]  (RotateLat, scripts/train_utils.py:124-125)."""
+    _begin("eeg_rotate_vec3")
+    _check(lib().eeg_rotate_vec3(_p(Q, f32), _p(graph_of, i64), _p(via, i64), _p(x, f32), _p(out, f32), C.c_int64(x.shape[0]), _stream()),
+           "eeg_rotate_vec3")
+
+
+def rotate_cart4_to_mandel(Q, C4, out):
+    """out[g] = Mandel(Q_g x4 C4[g])  (scripts/train_utils.py:122-123,133-134); Q None = no rotation."""
+    _begin("eeg_rotate_cart4_to_mandel")
+    _check(lib().eeg_rotate_cart4_to_mandel(_p(Q, f32), _p(C4, f32), _p(out, f32), C.c_int64(C4.shape[0]), _stream()),
+           "eeg_rotate_cart4_to_mandel")
+
+
+def validation_metrics(pred, target, directions, per_lattice, eig_pred=None, eig_target=None):
+    """per_lattice[g] = (mse, l1, dir_loss, mean_stiffness); optional ascending eigenvalues (scripts/train_utils.py:149-172)."""
+    _begin("eeg_validation_metrics")
+    _check(lib().eeg_validation_metrics(_p(pred, f32), _p(target, f32), _p(directions, f32), C.c_int(directions.shape[0]),
+                                        C.c_int64(pred.shape[0]), _p(per_lattice, f32), _p(eig_pred, f32), _p(eig_target, f32),
+                                        _stream()), "eeg_validation_metrics")

@@ -183,6 +183,25 @@ int eeg_adamw_step(float* p, const float* g, float* m, float* v, float* vmax, in
                    float eps, float weight_decay, int step, const float* gnorm_sq, float max_norm, float grad_scale,
                    void* stream);
 
+/* ---- RotateLat on a collated batch (scripts/train_utils.py:114-146).  Q = [G,3,3] row-major, one
+ * proper rotation per lattice.  eeg_rotate_vec3: out[i] = Q[graph_of[via ? via[i] : i]] . in[i] for n rows of 3 floats
+ * (positions: graph_of = batch, via = NULL (:124); shifts: via = edge_index row 0, the sender (:125)); in == out is allowed.
+ * eeg_rotate_cart4_to_mandel: C4 [G,3,3,3,3] -> Q_ai Q_bj Q_ck Q_dl C_ijkl (:122-123) -> Mandel [G,6,6]
+ * (lattices/lattices/utils/elasticity_func.py:406-428, the conversion RotateLat applies at :133-134); Q NULL = no
+ * rotation (RotateLat(rotate=False), :126-131). */
+int eeg_rotate_vec3(const float* Q, const int64_t* graph_of, const int64_t* via, const float* in, float* out, int64_t n,
+                    void* stream);
+int eeg_rotate_cart4_to_mandel(const float* Q, const float* C4, float* out, int64_t G, void* stream);
+
+/* ---- validation / test metrics (scripts/train_utils.py:66-89 validation_step, :149-172 obtain_errors; SURVEY.md 8(f)
+ * rank 3).  pred, target: Mandel [G,6,6]; directions: [P,3] unit vectors.  per_lattice [G,4] = (mean squared error and mean
+ * absolute error over the 36 entries (:157-158), mean_p |c(d_p) - c_pred(d_p)| (:161-163), mean_p c(d_p) of the target
+ * (:164)) with c(d) = C_ijkl d_i d_j d_k d_l of the Mandel -> Cartesian expansion of
+ * lattices/lattices/utils/elasticity_func.py:430-463.  eig_pred / eig_target [G,6] (either may be NULL): ascending
+ * eigenvalues as torch.linalg.eigvalsh returns them (:166-170). */
+int eeg_validation_metrics(const float* pred, const float* target, const float* directions, int P, int64_t G,
+                           float* per_lattice, float* eig_pred, float* eig_target, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
