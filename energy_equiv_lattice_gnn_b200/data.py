@@ -70,6 +70,8 @@ def collate(data_list: Sequence[LatticeData]) -> Batch:
     )
     if all(d.stiffness is not None for d in data_list):
         b.stiffness = torch.cat([d.stiffness for d in data_list], 0)
+    if all(getattr(d, "compliance", None) is not None for d in data_list):  # catalogue.process_one output
+        b.compliance = torch.cat([d.compliance for d in data_list], 0)
     return b
 
 
