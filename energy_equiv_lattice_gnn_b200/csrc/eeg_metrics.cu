@@ -8,55 +8,11 @@
 // number is v^T U v with v = (d0^2, d1^2, d2^2, sqrt2 d1 d2, sqrt2 d0 d2, sqrt2 d0 d1) and U the upper triangle counted
 // twice off the diagonal, 21 terms.
 #include "eeg_common.cuh"
+#include "eeg_eig6.cuh"
 
 namespace {
 
 constexpr int MW = 4;  // lattices (warps) per CTA
-
-// cyclic Jacobi on a 6x6 symmetric matrix (one thread); eigenvalues sorted ascending
-__device__ void eigvalsh6(const float* __restrict__ src, float* __restrict__ ev) {
-  float a[6][6];
-  for (int i = 0; i < 6; ++i)
-    for (int j = 0; j <= i; ++j) a[i][j] = a[j][i] = src[i * 6 + j];  // lower triangle, like LAPACK 'L' behind eigvalsh
-  for (int sweep = 0; sweep < 12; ++sweep) {
-    float off = 0.f, diag = 0.f;
-    for (int i = 0; i < 6; ++i) {
-      diag += a[i][i] * a[i][i];
-      for (int j = 0; j < i; ++j) off += a[i][j] * a[i][j];
-    }
-    if (off <= 1e-16f * diag) break;
-    for (int p = 0; p < 5; ++p)
-      for (int q = p + 1; q < 6; ++q) {
-        const float apq = a[p][q];
-        if (apq == 0.f) continue;
-        const float theta = (a[q][q] - a[p][p]) / (2.f * apq);
-        const float t = (theta >= 0.f ? 1.f : -1.f) / (fabsf(theta) + sqrtf(fmaf(theta, theta, 1.f)));
-        const float c = rsqrtf(fmaf(t, t, 1.f)), s = t * c;
-        for (int k = 0; k < 6; ++k) {
-          const float akp = a[k][p], akq = a[k][q];
-          a[k][p] = c * akp - s * akq;
-          a[k][q] = s * akp + c * akq;
-        }
-        for (int k = 0; k < 6; ++k) {
-          const float apk = a[p][k], aqk = a[q][k];
-          a[p][k] = c * apk - s * aqk;
-          a[q][k] = s * apk + c * aqk;
-        }
-      }
-  }
-  float e[6];
-  for (int i = 0; i < 6; ++i) e[i] = a[i][i];
-  for (int i = 1; i < 6; ++i) {
-    const float v = e[i];
-    int j = i - 1;
-    while (j >= 0 && e[j] > v) {
-      e[j + 1] = e[j];
-      --j;
-    }
-    e[j + 1] = v;
-  }
-  for (int i = 0; i < 6; ++i) ev[i] = e[i];
-}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -112,8 +68,8 @@ __global__ void __launch_bounds__(MW * 32) k_validation_metrics(const float* __r
     o[2] = P > 0 ? dl / (float)P : 0.f;
     o[3] = P > 0 ? ms / (float)P : 0.f;
   }
-  if (lane == 0 && eig_pred) eigvalsh6(Cp, eig_pred + g * 6);
-  if (lane == 1 && eig_target) eigvalsh6(Ct, eig_target + g * 6);
+  if (lane == 0 && eig_pred) eeg_eigvalsh6(Cp, eig_pred + g * 6);
+  if (lane == 1 && eig_target) eeg_eigvalsh6(Ct, eig_target + g * 6);
 }
 
 }  // namespace
