@@ -1,4 +1,11 @@
-# round-1 session-13 GPU pass: full gpu tests, bench line, ncu full capture of the TP forward (default launch order)
-python -m pytest tests -m gpu -x -q > gpurun_out/r01_gpu_tests_s13b.log 2>&1; tail -3 gpurun_out/r01_gpu_tests_s13b.log
-python bench.py > gpurun_out/r01_bench_s13b.json 2> gpurun_out/bench.err; cut -c1-200 gpurun_out/r01_bench_s13b.json; tail -c 400 gpurun_out/bench.err
-ncu --set full --clock-control none --import-source on -k regex:k_tp_scatter -c 2 -o gpurun_out/r01_tp_fwd_s13c -f python bench.py --no-train --no-cpu-baseline --steps 1 --warmup 0 > gpurun_out/ncu_full.log 2>&1; tail -2 gpurun_out/ncu_full.log
+# A/B timing of the TP forward launch order / L2 hints on one B200 (EEG_TP_MODE bit 0 = wave-interleaved output-l groups,
+# bit 1 = L2 eviction hints; EEG_TP_WAVE = CTAs per wave).  Results of round 1: eeg_tp.cu launch_tp comment.
+for cfg in "0 0" "2 0" "3 444" "3 296" "3 888"; do
+  set -- $cfg
+  EEG_TP_MODE=$1 EEG_TP_WAVE=$2 python bench.py --no-train --no-cpu-baseline --steps 20 --warmup 5 > gpurun_out/ab_tp_$1_$2.json 2>gpurun_out/ab_tp.err
+  python - <<PY
+import json
+d=json.load(open("gpurun_out/ab_tp_$1_$2.json"))
+print("mode $1 wave $2", d["ms_per_step"], {k:v["ms"] for k,v in d["kernels"].items() if "tp_scatter" in k})
+PY
+done
