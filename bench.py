@@ -134,7 +134,30 @@ def ncu_traffic(tag, n_nodes, n_edges):
     return ent["dram_bytes_read"] + ent["dram_bytes_write"], ent.get("source")
 
 
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """stdout must hold exactly ONE JSON line: point fd 1 at stderr for the whole run (NCCL prints its version banner to
+    stdout from C at NCCL_DEBUG >= VERSION, libraries may print warnings) and keep the real stdout for `_emit`."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line: dict):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    _guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -181,7 +204,7 @@ def main():
                                            "reference formulation (dense w3j tensor product, U.W.x contraction), torch fp32"},
                 "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line))
+        _emit(line)
         return
 
     if not torch.cuda.is_available():
@@ -361,7 +384,7 @@ def main():
         line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": thr, "kind": "port", "ms_per_step": ms,
                                 "sample": f"{CPU_SAMPLE} lattices/step (seeds 2000..{2000 + CPU_SAMPLE - 1}) of the same workload, 1 warm-up + 3 timed, "
                                           "oracle/ CPU restatement of the reference formulation, torch fp32"}
-    print(json.dumps(line))
+    _emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
