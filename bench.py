@@ -315,7 +315,10 @@ def main():
     step_sum = sum(kern.values())
     alg = algorithmic_model(model, n_nodes, n_edges)
     peak, peak_src = measured_peaks()
-    top = max((k for k in kern if k in alg), key=lambda k: kern[k])
+    # dominant kernel among the memory-streaming ones (north_star: message / scatter kernels vs the HBM roofline); the
+    # symmetric contraction is fp32-FMA bound with ~0.2 GB of traffic, a bytes roofline says nothing about it - it is listed
+    # with its TFLOP/s under "kernels" (68.3 TFLOP/s measured FFMA2 peak)
+    top = max((k for k in kern if k in alg and "sym_contract" not in k), key=lambda k: kern[k])
     top_ms = kern[top]
     achieved = alg[top]["bytes"] / (top_ms * 1e-3) / 1e9
     traffic, traffic_src = ncu_traffic(top, n_nodes, n_edges)
