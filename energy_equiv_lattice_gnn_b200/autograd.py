@@ -140,6 +140,8 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         grads[id(inter.linear.bias)] = gb
         inv_norm = 1.0 / model.agg_norm_const   # folded into dM so that the TP backward needs no rescaling pass
         dM = nv.block_linear(dmsg, model._lay_h, Wi, woff, [sc * inv_norm for sc in iscale], model._lay_M[i], N, transB=True)
+        if model.interaction_reduction == "mean":
+            nv.scale_rows_inv_degree(dM, sv["row_ptr"])
         # tensor product + scatter
         nv.set_tag(f'bwd.L{i}.tp_scatter')
         dw, dhup = nv.tp_scatter_bwd(0 if i == 0 else lmax, lmax, C, sv["hup"][i], sv["Y"], sv["w"][i], sv["snd"], sv["row_ptr"],

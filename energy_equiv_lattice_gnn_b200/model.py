@@ -48,8 +48,9 @@ class EnergyEquivGNN(torch.nn.Module):
             raise NotImplementedError("readout_irreps must have one entry per l = 0..lmax with parity (-1)^l")
         if C % 32 != 0:
             raise NotImplementedError("channel count must be a multiple of 32 (one warp lane per channel)")
-        if params.interaction_reduction.lower() != "sum":
-            raise NotImplementedError("interaction_reduction: only 'sum' is built (reference default, train_main.py:31)")
+        if params.interaction_reduction.lower() not in ("sum", "mean"):
+            raise NotImplementedError("interaction_reduction: 'sum' (reference default, train_main.py:31) and 'mean' are built; 'pna' is not")
+        self.interaction_reduction = params.interaction_reduction.lower()
         if params.positive_function not in _POSITIVE:
             raise ValueError(f"Unknown positive function: {params.positive_function}")
         if params.global_reduction not in ("mean", "sum"):
@@ -254,6 +255,8 @@ class EnergyEquivGNN(torch.nn.Module):
             plan = self._tp[i]
             nv.set_tag(f'L{i}.tp_scatter')
             M = nv.tp_scatter(0 if i == 0 else lmax, lmax, C, hup, Y, w, snd, row_ptr, 1.0 / self.agg_norm_const, plan["rows_total"], N)
+            if self.interaction_reduction == "mean":   # torch_scatter reduce='mean' (gnn/blocks.py:595-597)
+                nv.scale_rows_inv_degree(M, row_ptr)
             n_l = [ps["n_paths"] for ps in plan["passes"]]
             woff = np.concatenate(([0], np.cumsum([n * C * C for n in n_l])))[:-1].tolist()
             nv.set_tag(f'L{i}.interaction_linear')

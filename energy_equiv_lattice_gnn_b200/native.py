@@ -22,7 +22,7 @@ SYMBOLS = [
     # explicit backward ops + optimizer
     "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
-    "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics",
+    "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
 ]
 
 
@@ -451,3 +451,10 @@ def validation_metrics(pred, target, directions, per_lattice, eig_pred=None, eig
     _check(lib().eeg_validation_metrics(_p(pred, f32), _p(target, f32), _p(directions, f32), C.c_int(directions.shape[0]),
                                         C.c_int64(pred.shape[0]), _p(per_lattice, f32), _p(eig_pred, f32), _p(eig_target, f32),
                                         _stream()), "eeg_validation_metrics")
+
+
+def scale_rows_inv_degree(x, row_ptr):
+    """x[n, :] /= max(in-degree(n), 1) in place (interaction_reduction='mean', gnn/blocks.py:595-597)."""
+    _begin("eeg_scale_rows_inv_degree")
+    _check(lib().eeg_scale_rows_inv_degree(_p(x, f32), _p(row_ptr, i32), C.c_int64(x.shape[0]), C.c_int64(x.numel() // max(x.shape[0], 1)),
+                                           _stream()), "eeg_scale_rows_inv_degree")

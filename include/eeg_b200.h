@@ -183,6 +183,11 @@ int eeg_adamw_step(float* p, const float* g, float* m, float* v, float* vmax, in
                    float eps, float weight_decay, int step, const float* gnorm_sq, float max_norm, float grad_scale,
                    void* stream);
 
+/* ---- interaction_reduction = 'mean' (gnn/blocks.py:595-597, torch_scatter reduce='mean'): x[n, :] /= max(in-degree(n), 1)
+ * in place, x = M[N, row_floats] after eeg_tp_scatter_fwd, or dM before eeg_tp_scatter_bwd (the scaling is its own adjoint).
+ * row_ptr = CSR by receiver (eeg_csr_build). */
+int eeg_scale_rows_inv_degree(float* x, const int32_t* row_ptr, int64_t N, int64_t row_floats, void* stream);
+
 /* ---- RotateLat on a collated batch (scripts/train_utils.py:114-146).  Q = [G,3,3] row-major, one
  * proper rotation per lattice.  eeg_rotate_vec3: out[i] = Q[graph_of[via ? via[i] : i]] . in[i] for n rows of 3 floats
  * (positions: graph_of = batch, via = NULL (:124); shifts: via = edge_index row 0, the sender (:125)); in == out is allowed.

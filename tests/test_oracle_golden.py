@@ -79,6 +79,16 @@ def test_oracle_variants_match_reference():
         assert rel(out, want) < 1e-12, key
 
 
+def test_oracle_interaction_mean_matches_reference():
+    """interaction_reduction='mean' (gnn/blocks.py:595-597), fixture from oracle/make_golden_mean.py."""
+    fx = load("ref_forward_lmax4.pt")
+    want = load("ref_interaction_mean.pt")["stiffness"]
+    m, b = oracle_from_fixture(fx, torch.float64, interaction_reduction="mean")
+    with torch.no_grad():
+        out = m(b)["stiffness"]
+    assert rel(out, want) < 1e-12
+
+
 def test_reference_tables_match_product_tables():
     with open(os.path.join(GOLD, "ref_tables.json")) as f:
         t = json.load(f)

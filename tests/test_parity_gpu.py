@@ -61,6 +61,19 @@ def test_variants_match_reference_golden(cuda_device):
     assert n >= 5
 
 
+def test_interaction_mean_matches_reference_golden(cuda_device):
+    """interaction_reduction='mean' (gnn/blocks.py:595-597): eeg_scale_rows_inv_degree after the TP scatter; the batch holds a
+    1-node lattice made of self-loops and nodes of different in-degree."""
+    fx = torch.load(os.path.join(GOLD, "ref_forward_lmax4.pt"), weights_only=False)
+    want = torch.load(os.path.join(GOLD, "ref_interaction_mean.pt"), weights_only=False)["stiffness"]
+    model = model_from_fixture(fx, cuda_device, interaction_reduction="mean")
+    with torch.no_grad():
+        out = model(Batch(**fx["batch"]).to(cuda_device))["stiffness"].cpu()
+    assert rel_err(out, want) < RTOL, rel_err(out, want)
+    with pytest.raises(NotImplementedError):
+        model_from_fixture(fx, cuda_device, interaction_reduction="pna")
+
+
 def test_forward_matches_oracle_config1(cuda_device):
     batch, rmax = synthetic_batch(range(1000, 1016))
     oracle, params = make_pair(rmax, dtype=torch.float64)
