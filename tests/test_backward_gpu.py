@@ -10,7 +10,6 @@ from tests.util import batch_to, cuda_model_from, make_pair
 
 pytestmark = pytest.mark.gpu
 GTOL = 2e-4
-UNVERIFIED = "not yet run on a B200 this round (pod had no free GPU slot at session end); remove once green"
 
 
 def _grads(lmax_over, n_lat, cuda_device, positive="matrix_power_2"):
@@ -32,8 +31,7 @@ def _grads(lmax_over, n_lat, cuda_device, positive="matrix_power_2"):
 @pytest.mark.parametrize("over,positive", [({}, "matrix_power_2"), ({}, "matrix_power_4"),
                                            (dict(lmax=3, hidden_irreps="32x0e+32x1o+32x2e+32x3o", readout_irreps="16x0e+16x1o+16x2e+16x3o"),
                                             "matrix_trunc_exp_2"),
-                                           pytest.param(dict(interaction_reduction="mean"), "matrix_power_2",
-                                                        marks=pytest.mark.xfail(strict=False, reason=UNVERIFIED))])
+                                           (dict(interaction_reduction="mean"), "matrix_power_2")])
 def test_parameter_gradients_match_oracle_autograd(cuda_device, over, positive):
     ref, got, ref_loss, loss = _grads(over, 6, cuda_device, positive)
     assert abs(loss - ref_loss) < 1e-5 * abs(ref_loss)

@@ -61,7 +61,6 @@ def test_variants_match_reference_golden(cuda_device):
     assert n >= 5
 
 
-@pytest.mark.xfail(strict=False, reason="not yet run on a B200 this round (pod had no free GPU slot at session end); remove once green")
 def test_interaction_mean_matches_reference_golden(cuda_device):
     """interaction_reduction='mean' (gnn/blocks.py:595-597): eeg_scale_rows_inv_degree after the TP scatter; the batch holds a
     1-node lattice made of self-loops and nodes of different in-degree."""

@@ -17,7 +17,6 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden", "ref_sample_cat.pt")
 
 
-@pytest.mark.xfail(strict=False, reason="not yet run on a B200 this round (pod had no free GPU slot at session end); remove once green")
 def test_real_lattices_rotate_predict_validate(cuda_device):
     cat = torch.load(GOLD, weights_only=False)
     # stiffness of the catalogue is ~1e-4 .. 1e-2 of the base material; the reference trains on multiples of it
