@@ -8,6 +8,7 @@
 // The input-gradient of a linear is eeg_block_linear_fwd with transB = 1 (dX = dY W^T).
 #include <math.h>
 #include "eeg_common.cuh"
+#include "eeg_eig6.cuh"
 
 namespace {
 
@@ -198,6 +199,38 @@ __global__ void __launch_bounds__(128) k_pool_tail_bwd(const float* __restrict__
   __syncthreads();
   if (P.positive == 0) {
     if (t < 36) dA[t] = dCs[t];
+  } else if (P.positive == 5) {
+    // adjoint of exp at symmetric A = V diag(ev) V^T:  dA = V [(V^T dC V) o Phi] V^T,  Phi_ij = (e^ev_i - e^ev_j) / (ev_i - ev_j)
+    float* ev = dA + 36;
+    if (t == 0) eeg_eigh6(A, ev, B);   // B = V
+    __syncthreads();
+    float s = 0.f;
+    if (t < 36) {   // dB = V^T dC
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s = fmaf(B[k * 6 + t / 6], dCs[k * 6 + t % 6], s);
+      dB[t] = s;
+    }
+    __syncthreads();
+    if (t < 36) {   // A <- (dB V) o Phi
+      s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s = fmaf(dB[(t / 6) * 6 + k], B[k * 6 + t % 6], s);
+      A[t] = s * eeg_exp_divdiff(ev[t / 6], ev[t % 6]);
+    }
+    __syncthreads();
+    if (t < 36) {   // dB = V A
+      s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s = fmaf(B[(t / 6) * 6 + k], A[k * 6 + t % 6], s);
+      dB[t] = s;
+    }
+    __syncthreads();
+    if (t < 36) {   // dA = dB V^T
+      s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s = fmaf(dB[(t / 6) * 6 + k], B[(t % 6) * 6 + k], s);
+      dA[t] = s;
+    }
   } else if (P.positive == 1) {
     mat6_sq_bwd(A, dCs, dA, t);
   } else {
@@ -396,12 +429,12 @@ extern "C" int eeg_pool_tail_bwd(const float* o, const EegLayout* lo, const int3
                                  const int32_t* host_qmul, const float* host_qscale, const float* P, int positive, int reduce,
                                  const float* A, const float* dC, float* d_o, float* dq_ws /*[G,nq]*/, float* pooled_ws /*[G,npool]*/,
                                  float* dWq, float* dbias, int64_t G, void* stream) {
-  EEG_REQUIRE(lo && lo->n_blocks <= EEG_MAX_L && positive >= 0 && positive <= 4, "eeg_pool_tail_bwd: bad arguments");
+  EEG_REQUIRE(lo && lo->n_blocks <= EEG_MAX_L && positive >= 0 && positive <= 5, "eeg_pool_tail_bwd: bad arguments");
   if (G == 0) return 0;
   TailBwdParams T;
   int n_w = 0;
   fill_tail(T, lo, host_qmul, host_qscale, positive, reduce, &n_w);
-  const size_t smem = (size_t)(T.npool + T.nq + 36 * 5) * sizeof(float);
+  const size_t smem = (size_t)(T.npool + T.nq + 36 * 5 + 8) * sizeof(float);
   EEG_REQUIRE(smem <= 48 * 1024, "eeg_pool_tail_bwd: pooled row too large");
   k_pool_tail_bwd<<<(unsigned)G, 128, smem, (cudaStream_t)stream>>>(o, graph_ptr, Wq, P, A, dC, d_o, dq_ws, pooled_ws, T);
   EEG_CHECK_LAUNCH("eeg_pool_tail_bwd");

@@ -28,4 +28,15 @@ void eeg_set_error(const char* fmt, ...);
 
 static inline int eeg_div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// cudaFuncSetAttribute applies per device: one "already opted in" flag per device ordinal, looked up with the device
+// that is current at launch time (a process may drive several GPUs).
+struct EegDevFlags {
+  bool f[64] = {};
+};
+static inline bool& eeg_dev_flag(EegDevFlags& fl) {
+  int d = 0;
+  cudaGetDevice(&d);
+  return fl.f[d & 63];
+}
+
 __device__ __forceinline__ float eeg_silu(float x) { return x / (1.0f + __expf(-x)); }

@@ -201,7 +201,7 @@ int eeg_lin32_launch(const float* in, const EegLayout* lin, const float* W, cons
     if (tiles >= (1LL << 31)) return -1;
   }
   if (tiles == 0) return 0;
-  static bool attr = false;
+  static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_lin32<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L32_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_lin32<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L32_SMEM);

@@ -217,7 +217,7 @@ int eeg_lin32_mma_launch(const float* in, const EegLayout* lin, const float* W, 
     }
   }
   const size_t smem = (size_t)ng * 2048 * sizeof(float);
-  static bool attr = false;
+  static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_lin32_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, LM_MAXG * 2048 * (int)sizeof(float));
     if (e != cudaSuccess) {

@@ -178,7 +178,7 @@ extern "C" int eeg_linear_pair_fwd(const float* x, const float* residual, const 
       P.warp_rank[w] = (unsigned char)r;
     }
   }
-  static bool attr = false;
+  static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_linpair_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, LP_MAXB * 32 * CM_FRAG * 4);
     if (e != cudaSuccess) {

@@ -301,7 +301,7 @@ extern "C" int eeg_radial_mlp_fwd(const float* f, int n_in, const float* W0, con
   EEG_REQUIRE(n_hidden >= 0 && n_hidden <= RM_MAX_HIDDEN, "eeg_radial_mlp_fwd: at most %d hidden layers (got %d)", RM_MAX_HIDDEN, n_hidden);
   EEG_REQUIRE(n_out > 0 && n_out % 32 == 0, "eeg_radial_mlp_fwd: output width must be a multiple of 32 (got %d)", n_out);
   if (E == 0) return 0;
-  static bool attr_set = false;
+  static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(k_radial_mlp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RadialSmem::TOTAL);
     if (e != cudaSuccess) {

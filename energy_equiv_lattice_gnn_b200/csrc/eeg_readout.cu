@@ -282,7 +282,7 @@ extern "C" int eeg_readout_chain_fwd(const float* B, const float* residual, cons
     d.s2 = host_s2[b];
     d.n_rt = eeg_div_up(N, RC_WARPS * RC_CHUNKS_PER_WARP * rc_npc(rows));
   }
-  static bool attr = false;
+  static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_readout_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, RC_SMEM);
     if (e != cudaSuccess) {

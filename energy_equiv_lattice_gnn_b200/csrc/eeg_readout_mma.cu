@@ -223,7 +223,7 @@ int eeg_readout_chain_mma_launch(const float* B, const float* residual, const Ee
     if (lout->mul[b] % 8 || lout->mul[b] < 8 || lout->mul[b] > 32 || (lout->off[b] & 1) || (lh->off[b] & 1)) return -1;
     if (N * lh->rows[b] >= (1LL << 28)) return -1;
   }
-  static bool attr = false;
+  static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_chain_mma<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_chain_mma<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);

@@ -115,7 +115,7 @@ template <int LMAX>
 int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float* dx, int64_t N, cudaStream_t s) {
   using F = ProgB<LMAX>;
   const size_t smem = (size_t)(CH * F::NCOEF + 2 * CH * F::D * NT) * sizeof(float);
-  static bool attr_set = false;
+  static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(k_sc_bwd_x<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {

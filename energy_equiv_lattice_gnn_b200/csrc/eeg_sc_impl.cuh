@@ -252,7 +252,7 @@ template <int LMAX>
 int launch_sc(int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s) {
   using F = Prog<LMAX>;
   const size_t smem = (size_t)SC_SMEM_FLOATS(F) * sizeof(float);
-  static bool attr_set = false;
+  static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(k_sym_contract<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {

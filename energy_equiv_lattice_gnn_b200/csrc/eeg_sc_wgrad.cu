@@ -136,7 +136,7 @@ template <int LMAX>
 int launch_wgrad(int C, const float* x, const float* dout, int64_t N, float* dT, cudaStream_t s) {
   constexpr int D = (LMAX + 1) * (LMAX + 1);
   constexpr size_t smem = (size_t)2 * 2 * WG_NB * D * 32 * sizeof(float);
-  static bool attr = false;
+  static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(k_sc_wgrad<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {

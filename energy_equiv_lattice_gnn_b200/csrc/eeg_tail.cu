@@ -2,6 +2,7 @@
 // scatter(mean) pooling (gnn/model.py:100-106) -> final o3.Linear (:108) -> Spherical_to_Cartesian + Cart_4_to_Mandel
 // (gnn/blocks.py:392-442, folded into one [n_q, 36] matrix) -> PositiveLayer (gnn/blocks.py:185-229).
 #include "eeg_common.cuh"
+#include "eeg_eig6.cuh"
 
 namespace {
 
@@ -130,6 +131,18 @@ __global__ void __launch_bounds__(128) k_pool_tail(const float* __restrict__ o, 
       res = Cm;
     }
   }
+  else if (P.positive == 5) {  // exp(A), A symmetric: V diag(exp(ev)) V^T
+    if (t == 0) eeg_eigh6(A, Cm, B);   // Cm[0..5] = eigenvalues, B = V
+    __syncthreads();
+    float s = 0.f;
+    if (t < 36) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) s = fmaf(B[(t / 6) * 6 + k] * expf(Cm[k]), B[(t % 6) * 6 + k], s);
+    }
+    __syncthreads();
+    if (t < 36) Cm[t] = s;
+    res = Cm;
+  }
   __syncthreads();
   if (t < 36) C_out[(int64_t)g * 36 + t] = res[t];
 }
@@ -164,7 +177,7 @@ extern "C" int eeg_pool_tail_fwd(const float* o, const EegLayout* lo, const int3
                                  const int32_t* host_qmul, const float* host_qscale, const float* bias, const float* P,
                                  int positive, int reduce, float* q_out, float* A_out, float* C_out, int64_t G, void* stream) {
   EEG_REQUIRE(lo && lo->n_blocks <= EEG_MAX_L, "eeg_pool_tail_fwd: bad layout");
-  EEG_REQUIRE(positive >= 0 && positive <= 4, "eeg_pool_tail_fwd: unsupported positive function %d", positive);
+  EEG_REQUIRE(positive >= 0 && positive <= 5, "eeg_pool_tail_fwd: unsupported positive function %d", positive);
   if (G == 0) return 0;
   TailParams T;
   T.lo = *lo;

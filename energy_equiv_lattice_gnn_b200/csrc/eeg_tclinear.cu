@@ -378,7 +378,7 @@ int eeg_tc_linear_launch(const float* in, const EegLayout* lin, const float* W, 
   static const int cap = getenv("EEG_TC_STAGES") ? atoi(getenv("EEG_TC_STAGES")) : TL_MAX_STAGES;  // debugging knob
   if (P.stages > cap && cap >= 1) P.stages = cap;
   const size_t smem = (size_t)P.stages * TL_STAGE_BYTES + P.w_bytes + fixed;
-  static bool attr_set = false;
+  static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(k_tc_linear, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TL_SMEM_BUDGET);
     if (e != cudaSuccess) {

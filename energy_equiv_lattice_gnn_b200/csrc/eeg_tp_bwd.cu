@@ -93,7 +93,7 @@ int launch_tpb(const float* h, const float* Y, int ystride, const float* w_t, in
                float inv_norm, const float* dM, float* dw, float* dh, int64_t N, int C, cudaStream_t s) {
   using I = TpB<LIN, LMAX>;
   const size_t smem = (size_t)I::NTAB * 16 + (size_t)WARPS * I::NTAB * 4;
-  static bool attr_set = false;
+  static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set && smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(k_tp_bwd<LIN, LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {

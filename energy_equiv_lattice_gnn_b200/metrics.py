@@ -42,15 +42,31 @@ def per_lattice_metrics(pred: torch.Tensor, target: torch.Tensor, directions: to
     return out, ep, et
 
 
-def validation_step(model, batch, directions: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+def validation_step(model, batch, directions: Optional[torch.Tensor] = None, process_group=None,
+                    sync_dist: bool = True) -> Dict[str, torch.Tensor]:
     """`LightningWrappedModel.validation_step` (train_utils.py:66-89): MSE over all entries and the L1 error of the
-    directional stiffness over 250 random directions.  Returns 0-dim CUDA tensors (no host sync)."""
+    directional stiffness over 250 random directions.  Returns 0-dim CUDA tensors (no host sync).
+    With an initialised process group and sync_dist (the reference logs with `sync_dist=True`, train_utils.py:87-88) the two
+    scalars are averaged over the ranks with ONE all-reduce of a 2-float tensor."""
     if directions is None:
         directions = random_directions()
     with torch.no_grad():
         pred = model(batch)["stiffness"]
         m, _, _ = per_lattice_metrics(pred, batch["stiffness"], directions, eigenvalues=False)
-    return {"val_loss": m[:, 0].mean(), "val_stiff_dir_loss": m[:, 2].mean()}
+    vals = torch.stack([m[:, 0].mean(), m[:, 2].mean()])
+    vals = sync_validation_scalars(vals, process_group) if sync_dist else vals
+    return {"val_loss": vals[0], "val_stiff_dir_loss": vals[1]}
+
+
+def sync_validation_scalars(vals: torch.Tensor, process_group=None) -> torch.Tensor:
+    """Lightning `self.log(..., sync_dist=True)`: mean over ranks (device-agnostic: used with gloo in the CPU tests)."""
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        world = torch.distributed.get_world_size(process_group)
+        if world > 1:
+            vals = vals.clone()
+            torch.distributed.all_reduce(vals, op=torch.distributed.ReduceOp.SUM, group=process_group)
+            vals = vals / world
+    return vals
 
 
 def obtain_errors(results: Sequence, tag: str, directions: Optional[torch.Tensor] = None) -> Dict[str, np.ndarray]:

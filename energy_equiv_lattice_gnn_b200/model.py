@@ -21,7 +21,8 @@ from . import tables as tb
 
 NORM2MOM_SILU = 1.6791767923989418  # e3nn normalize2mom(silu), SURVEY.md B.5
 
-_POSITIVE = {"none": 0, "matrix_power_2": 1, "matrix_power_4": 2, "matrix_trunc_exp_2": 3, "matrix_trunc_exp_4": 4}
+_POSITIVE = {"none": 0, "matrix_power_2": 1, "matrix_power_4": 2, "matrix_trunc_exp_2": 3, "matrix_trunc_exp_4": 4,
+             "matrix_exp": 5}   # gnn/blocks.py:186-208
 
 
 class _Holder(torch.nn.Module):

@@ -458,3 +458,45 @@ def scale_rows_inv_degree(x, row_ptr):
     _begin("eeg_scale_rows_inv_degree")
     _check(lib().eeg_scale_rows_inv_degree(_p(x, f32), _p(row_ptr, i32), C.c_int64(x.shape[0]), C.c_int64(x.numel() // max(x.shape[0], 1)),
                                            _stream()), "eeg_scale_rows_inv_degree")
+
+
+# ---- device guard -----------------------------------------------------------------------------------------------------
+# The C-ABI launchers run on the CUDA device that is current in the calling thread and take the stream they are given.
+# Every binding above therefore runs with the device of its first CUDA tensor argument made current (so `_stream()` is
+# that device's current stream and the launch, its >48 KB shared-memory opt-ins included, lands on the tensors' device
+# even when the caller never called torch.cuda.set_device).
+def _first_cuda_device(args, kwargs):
+    for a in list(args) + list(kwargs.values()):
+        if isinstance(a, torch.Tensor) and a.is_cuda:
+            return a.device
+        if isinstance(a, (list, tuple)):
+            for b in a:
+                if isinstance(b, torch.Tensor) and b.is_cuda:
+                    return b.device
+    return None
+
+
+def _guarded(fn):
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        dev = _first_cuda_device(args, kwargs)
+        if dev is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+    return wrapper
+
+
+def _install_guards():
+    import inspect
+    g = globals()
+    skip = {"lib", "make_layout", "set_tag", "start_profile", "stop_profile"}
+    for name, fn in list(g.items()):
+        if name.startswith("_") or name in skip or not inspect.isfunction(fn) or fn.__module__ != __name__:
+            continue
+        g[name] = _guarded(fn)
+
+
+_install_guards()

@@ -49,6 +49,7 @@ class FlatAdamW:
 
     def __init__(self, model: torch.nn.Module, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=1e-2, amsgrad=True,
                  clip_norm: Optional[float] = 10.0):
+        self.model = model
         self.params = [p for p in model.parameters() if p.requires_grad]
         dev = self.params[0].device
         if dev.type != "cuda":
@@ -94,25 +95,61 @@ class FlatAdamW:
             gn = self.gnorm_sq
         nv.adamw_step(self.flat, self.grad, self.m, self.v, self.vmax, self.lr, self.b1, self.b2, self.eps, self.wd, self.t, gn,
                       self.clip or 0.0, scale)
+        # the kernel rewrote the parameters behind torch's version counters: drop the model's weight-derived tables
+        # (SC Horner coefficients, radial tcgen05 operand image) here, so FlatAdamW is safe to use without Trainer
+        bump = getattr(self.model, "_cache_bump", None)
+        if bump is not None:
+            bump()
         return self
 
 
 class Trainer:
-    """training_step of scripts/train_utils.py:45-64 + optimizer step; DDP = one flat all-reduce (sum) per step."""
+    """training_step of scripts/train_utils.py:45-64 + optimizer step; DDP = one flat all-reduce (sum) per optimizer step.
 
-    def __init__(self, model, lr=1e-3, beta1=0.9, eps=1e-8, weight_decay=1e-8, amsgrad=True, clip_norm=10.0, process_group=None):
+    accumulate_grad_batches = Lightning's Trainer(accumulate_grad_batches=k) (scripts/train_main.py:91, k = 4 there): the
+    loss of each micro-batch is scaled by 1/k before the backward, gradients add up in the flat buffer, and the all-reduce,
+    the clip and the AdamW step run after every k-th micro-batch.
+    global_mean = False reproduces the reference exactly (per-rank mean loss, DDP gradient MEAN over ranks: identical to the
+    global-batch gradient only for equal-sized shards); True weights each rank by its graph count, so edge-balanced shards
+    of unequal size (sharding.shard_batch) still give the gradient of the global-mean loss."""
+
+    def __init__(self, model, lr=1e-3, beta1=0.9, eps=1e-8, weight_decay=1e-8, amsgrad=True, clip_norm=10.0, process_group=None,
+                 accumulate_grad_batches: int = 1, global_mean: bool = False):
         self.model = model
         self.opt = FlatAdamW(model, lr=lr, beta1=beta1, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad, clip_norm=clip_norm)
         self.pg = process_group
+        self.accumulate = max(int(accumulate_grad_batches), 1)
+        self.global_mean = bool(global_mean)
+        self._micro = 0
+        self._count = None   # graphs accumulated since the last optimizer step (global_mean only)
+
+    def _distributed(self) -> bool:
+        return torch.distributed.is_available() and torch.distributed.is_initialized() and \
+            torch.distributed.get_world_size(self.pg) > 1
 
     def training_step(self, batch) -> torch.Tensor:
         self.model.train()
-        self.opt.zero_grad()
+        if self._micro == 0:
+            self.opt.zero_grad()
         out = self.model(batch)["stiffness"]
         loss = relative_mse_loss(out, batch.stiffness)
-        loss.backward()
+        n_local = float(out.shape[0])
+        # global_mean: back-propagate the SUM over this rank's lattices; divided by the global count at the step
+        scaled = loss * (n_local if self.global_mean else 1.0 / self.accumulate)
+        scaled.backward()
         self.opt.gather_grads()
+        if self.global_mean:
+            c = torch.tensor([n_local], dtype=torch.float64, device=out.device)
+            self._count = c if self._count is None else self._count + c
+        self._micro += 1
+        if self._micro < self.accumulate:
+            return loss.detach()
+        self._micro = 0
         world = sync_gradients(self.opt.grad, self.pg)
+        if self.global_mean:
+            if self._distributed():
+                torch.distributed.all_reduce(self._count, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+            self.opt.grad.mul_(float(world) / float(self._count.item()))   # step() divides by world again
+            self._count = None
         self.opt.step(world)
-        self.model._cache_bump()
         return loss.detach()

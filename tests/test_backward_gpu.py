@@ -31,7 +31,8 @@ def _grads(lmax_over, n_lat, cuda_device, positive="matrix_power_2"):
 @pytest.mark.parametrize("over,positive", [({}, "matrix_power_2"), ({}, "matrix_power_4"),
                                            (dict(lmax=3, hidden_irreps="32x0e+32x1o+32x2e+32x3o", readout_irreps="16x0e+16x1o+16x2e+16x3o"),
                                             "matrix_trunc_exp_2"),
-                                           (dict(interaction_reduction="mean"), "matrix_power_2")])
+                                           (dict(interaction_reduction="mean"), "matrix_power_2"),
+                                           ({}, "matrix_exp")])
 def test_parameter_gradients_match_oracle_autograd(cuda_device, over, positive):
     ref, got, ref_loss, loss = _grads(over, 6, cuda_device, positive)
     assert abs(loss - ref_loss) < 1e-5 * abs(ref_loss)

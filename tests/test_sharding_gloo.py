@@ -54,6 +54,10 @@ def _worker(rank, world, port, q):
     counts = [torch.tensor([g1 - g0]) for _ in range(world)]
     dist.all_gather(counts, torch.tensor([g1 - g0]))
     full = gather_stiffness(local, [int(c) for c in counts])
+    # validation scalars are averaged over ranks with one all-reduce (Lightning sync_dist=True, train_utils.py:87-88)
+    from energy_equiv_lattice_gnn_b200.metrics import sync_validation_scalars
+    vs = sync_validation_scalars(torch.tensor([rank + 1.0, 10.0 * (rank + 1)]))
+    assert torch.allclose(vs, torch.tensor([(world + 1) / 2.0, 5.0 * (world + 1)]))
     if rank == 0:
         with torch.no_grad():
             ref = m(to64(b))["stiffness"]
