@@ -16,8 +16,11 @@
 //   fill warps (8)  : A = G_e^T: each thread owns NIT fixed non-zeros (coefficients in registers), value = c0 Y[j0] + c1 Y[j1]
 //                     (Y held one value per lane, fetched by shuffles), split hi/lo, scattered into the zero-initialised
 //                     K-major tile; B = x[s]^T: coalesced rows of the sender, split hi/lo, K-major [32 x 16] tiles.
-//   loader (1 lane) : the edge's 42 x 128-byte per-path weight rows by cp.async.bulk (TMA engine) onto the slot's mbarrier.
-//   MMA (1 lane)    : 3 tcgen05.mma kind::tf32 per (tile, K-step of 8): A_hi B_hi + A_lo B_hi + A_hi B_lo -> TMEM.
+//   loader (1 warp) : per-path weight rows by cp.async.bulk (TMA engine), TU_WE consecutive edges per copy (w_t is path-major,
+//                     so the rows of consecutive CSR slots are contiguous) into a ring of TU_WG group buffers: the stream
+//                     from HBM runs 2-3 groups ahead of the compute (a 128-byte copy per (edge, path) was issue bound).
+//   MMA (1 lane)    : 2 tcgen05.mma kind::tf32 per (tile, K-step of 8): A_hi [B_hi | B_lo] (N = 64) + A_lo B_hi (N = 32): the A tile,
+//                     which dominates the operand traffic of these skinny products, is read twice instead of three times.
 //   epilogue (8)    : thread = TMEM lane = message row (p,k): tcgen05.ld the 32 channels, multiply by w[e,p,:], accumulate
 //                     over the receiver's edges in registers (CSR order: deterministic), and at the end of a node write
 //                     the row scaled by 1/agg_norm_const through a per-warp transpose tile with full-line stores.
@@ -33,8 +36,10 @@ using namespace eeg_umma;
 constexpr int TU_C = 32;                       // channels (= N of the MMA = lanes of a feature row)
 constexpr int TU_FILL_WARPS = EEG_TPU_FILL_THREADS / 32;
 constexpr int TU_SLOTS = 3;
-constexpr uint32_t TU_B_LBO = TU_C * 16;       // bytes between 4-float K-chunks of a [32 x KT] B tile
-constexpr int TU_W_PITCH = 144;                // bytes per staged weight row (128 + 16: rows of different paths -> different banks)
+constexpr uint32_t TU_B_LBO = 2 * TU_C * 16;   // bytes between 4-float K-chunks of a [64 x KT] B tile (rows 0-31 x_hi, 32-63 x_lo)
+constexpr int TU_WE = 4;                       // edges per weight copy (one bulk copy = TU_WE x 128 B of one path)
+constexpr int TU_WG = 3;                       // weight group buffers in flight
+constexpr int TU_W_PITCH = TU_WE * 128 + 16;   // bytes per path in a group buffer (+16: rows of different paths -> different banks)
 constexpr int TU_STG_LD = 36;                  // floats per row of the flush transpose tile
 
 template <int LIN, int LMAX>
@@ -60,20 +65,33 @@ struct TuCfg {
   static constexpr int FILL_WARP0 = EPI_WARPS, MMA_WARP = EPI_WARPS + TU_FILL_WARPS, LOAD_WARP = MMA_WARP + 1;
   static constexpr int THREADS = (LOAD_WARP + 1) * 32;
   static constexpr uint32_t A_TILE = KCH * EEG_TPU_A_LBO, A_TERM = NT * A_TILE, A_BYTES = 2 * A_TERM;
-  static constexpr uint32_t B_TILE = KCH * TU_B_LBO, B_TERM = NT * B_TILE, B_BYTES = 2 * B_TERM;
-  static constexpr uint32_t W_BYTES = (I::NPATHS * TU_W_PITCH + 127) / 128 * 128;
-  static constexpr uint32_t SLOT_BYTES = A_BYTES + B_BYTES + W_BYTES;
+  static constexpr uint32_t B_TILE = KCH * TU_B_LBO, B_BYTES = NT * B_TILE, B_LO = TU_C * 16;   // lo rows follow the hi rows
+  static constexpr uint32_t W_BYTES = (I::NPATHS * TU_W_PITCH + 127) / 128 * 128;   // one weight group buffer
+  static constexpr uint32_t SLOT_BYTES = A_BYTES + B_BYTES;
   static constexpr uint32_t STG_BYTES = EPI_WARPS * 32 * TU_STG_LD * 4;
   static constexpr uint32_t ROWTAB_BYTES = NT * 128 * 8;
-  static constexpr uint32_t BAR_OFF = TU_SLOTS * SLOT_BYTES + STG_BYTES + ROWTAB_BYTES;
-  static constexpr uint32_t SMEM_BYTES = BAR_OFF + 128;
-  static constexpr int D_COLS = NT * TU_C;                 // TMEM columns per slot
-  static constexpr int TMEM_COLS = TU_SLOTS * D_COLS <= 128 ? 128 : 256;
+  static constexpr uint32_t W_OFF = TU_SLOTS * SLOT_BYTES;
+  static constexpr uint32_t STG_OFF = W_OFF + TU_WG * W_BYTES;
+  static constexpr uint32_t BAR_OFF = STG_OFF + STG_BYTES + ROWTAB_BYTES;
+  static constexpr uint32_t SMEM_BYTES = BAR_OFF + 256;
+  static constexpr int D_COLS = NT * 2 * TU_C;             // TMEM columns per slot: per tile [hi.hi + lo.hi | hi.lo]
+  static constexpr int TMEM_COLS = TU_SLOTS * D_COLS <= 128 ? 128 : (TU_SLOTS * D_COLS <= 256 ? 256 : 512);
   static constexpr int XCHUNKS = NT * KCH;                 // [tile][K-chunk of 4 components] pieces of the B operand
-  static_assert(TU_SLOTS * D_COLS <= 256, "TMEM budget");
+  static_assert(TU_SLOTS * D_COLS <= 512, "TMEM budget");
   static_assert(A_TERM % 16 == 0 && SLOT_BYTES % 128 == 0, "alignment");
   static_assert(XCHUNKS <= TU_FILL_WARPS, "one B chunk per fill warp");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+};
+
+// Optional per-role stall accounting (EEG_TP_PROF=1; read back with eeg_tp_umma_prof_read): clock64 spent in each wait site
+// of CTA b, by ONE lane per role.  Slots: 0 fill.wait_slot 1 fill.total 2 mma.wait_filled 3 mma.total 4 epi.wait_w
+// 5 epi.wait_d 6 epi.flush 7 epi.total 8 load.wait_free 9 load.total 10 edges 11 nodes
+__device__ unsigned long long eeg_tpu_prof[EEG_NUM_SMS * 16];
+template <bool PROF>
+struct TuTimer {
+  long long t0 = 0;
+  __device__ __forceinline__ void start() { if (PROF) t0 = clock64(); }
+  __device__ __forceinline__ void stop(unsigned long long& acc) { if (PROF) acc += (unsigned long long)(clock64() - t0); }
 };
 
 template <int SLEEP_NS>
@@ -96,7 +114,7 @@ __device__ __forceinline__ int64_t tu_lower_bound(const int32_t* __restrict__ ro
   return lo;
 }
 
-template <int LIN, int LMAX>
+template <int LIN, int LMAX, bool PROF>
 __global__ void __launch_bounds__(TuCfg<LIN, LMAX>::THREADS, 1)
 k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride, const float* __restrict__ w_t, int64_t E,
           const int32_t* __restrict__ sender, const int32_t* __restrict__ row_ptr, float inv_norm, float* __restrict__ M, int64_t N) {
@@ -106,20 +124,32 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
   constexpr int DIN = (LIN + 1) * (LIN + 1);
   extern __shared__ __align__(1024) uint8_t tu_smem[];
   uint8_t* const slots = tu_smem;
-  float* const stg_all = reinterpret_cast<float*>(tu_smem + S * CF::SLOT_BYTES);
-  int2* const rowtab = reinterpret_cast<int2*>(tu_smem + S * CF::SLOT_BYTES + CF::STG_BYTES);
+  uint8_t* const wbufs = tu_smem + CF::W_OFF;
+  float* const stg_all = reinterpret_cast<float*>(tu_smem + CF::STG_OFF);
+  int2* const rowtab = reinterpret_cast<int2*>(tu_smem + CF::STG_OFF + CF::STG_BYTES);
   uint64_t* const bars = reinterpret_cast<uint64_t*>(tu_smem + CF::BAR_OFF);
-  uint64_t* const filled = bars;              // [S] fill threads + loader (with the weight bytes) -> MMA, epilogue
+  uint64_t* const filled = bars;              // [S] fill threads -> MMA
   uint64_t* const d_full = bars + S;          // [S] MMA commit -> epilogue
-  uint64_t* const slot_free = bars + 2 * S;   // [S] epilogue -> fill, loader
-  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * S);
+  uint64_t* const slot_free = bars + 2 * S;   // [S] epilogue -> fill
+  uint64_t* const w_full = bars + 3 * S;      // [TU_WG] loader (expect_tx + bulk copies) -> epilogue
+  uint64_t* const w_free = w_full + TU_WG;    // [TU_WG] epilogue -> loader
+  uint32_t* const tmem_slot = reinterpret_cast<uint32_t*>(w_free + TU_WG);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  unsigned long long pw0 = 0, pw1 = 0, pw2 = 0, ptot = 0;   // PROF accumulators of this thread
+  TuTimer<PROF> tw, tt;
+  unsigned long long* const prof = eeg_tpu_prof + (blockIdx.x % EEG_NUM_SMS) * 16;
 
   if (tid == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(&filled[s], EEG_TPU_FILL_THREADS + 1);
+      // one arrival per WARP (lane 0 after __syncwarp): 256 per-thread arrivals on one barrier word serialise in the
+      // shared-memory atomic unit (~32 clk per warp instruction) and cost ~250 clk per edge in the first version
+      mbar_init(&filled[s], TU_FILL_WARPS);
       mbar_init(&d_full[s], 1);
-      mbar_init(&slot_free[s], CF::EPI_WARPS * 32);
+      mbar_init(&slot_free[s], CF::EPI_WARPS);
+    }
+    for (int b = 0; b < TU_WG; ++b) {
+      mbar_init(&w_full[b], 1);
+      mbar_init(&w_free[b], CF::EPI_WARPS);
     }
     mbar_fence_init();
   }
@@ -141,13 +171,17 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
   const int64_t n_hi = blockIdx.x + 1 == gridDim.x ? N : tu_lower_bound(row_ptr, N, E * (blockIdx.x + 1) / gridDim.x);
   const int e_lo = n_lo < n_hi ? __ldg(row_ptr + n_lo) : 0, e_hi = n_lo < n_hi ? __ldg(row_ptr + n_hi) : 0;
   const uint32_t n_e = (uint32_t)(e_hi - e_lo);
+  // weight groups: TU_WE consecutive CSR slots, aligned to absolute slot index (a group may start before e_lo)
+  const int wg0 = e_lo / TU_WE;
+  const uint32_t n_wg = n_e ? (uint32_t)((e_hi - 1) / TU_WE - wg0 + 1) : 0u;
 
   if (warp < CF::EPI_WARPS) {
     // ======================================================= epilogue: thread = TMEM lane = message row (p, k)
     const int tile = warp >> 2, quad = warp & 3;
     const int2 info = rowtab[tile * 128 + quad * 32 + lane];
     const uint32_t wrow = (uint32_t)(info.x < 0 ? 0 : info.x) * TU_W_PITCH;
-    const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + tile * TU_C;
+    int wk_cur = -1;   // weight group (relative to wg0) this thread has acquired
+    const uint32_t taddr0 = tmem_base + ((uint32_t)(quad * 32) << 16) + tile * 2 * TU_C;
     float* const stg = stg_all + warp * (32 * TU_STG_LD);
     const int r4 = lane >> 3, q = lane & 7;
     float acc[TU_C];
@@ -155,30 +189,50 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
     for (int j = 0; j < TU_C; ++j) acc[j] = 0.f;
     uint32_t it = 0;
     int ee = e_lo;
+    tt.start();
     for (int64_t n = n_lo; n < n_hi; ++n) {
       const int eb = ee;
       ee = __ldg(row_ptr + n + 1);
       for (int e = eb; e < ee; ++e, ++it) {
         const uint32_t s = it % S, ph = (it / S) & 1;
-        const uint8_t* wsm = slots + (size_t)s * CF::SLOT_BYTES + CF::A_BYTES + CF::B_BYTES + wrow;
-        tu_wait<0>(&filled[s], ph);   // the weight rows were written through the async proxy onto this barrier
+        const int wk = e / TU_WE - wg0, wb = wk % TU_WG;
+        if (wk != wk_cur) {   // first edge of a weight group: the bulk copies land on w_full
+          tw.start();
+          tu_wait<0>(&w_full[wb], (uint32_t)(wk / TU_WG) & 1);
+          tw.stop(pw0);
+          wk_cur = wk;
+        }
+        const uint8_t* wsm = wbufs + (size_t)wb * CF::W_BYTES + wrow + (e % TU_WE) * 128;
+        tw.start();
         tu_wait<0>(&d_full[s], ph);
+        tw.stop(pw1);
         tc_fence_after_sync();
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(taddr0 + s * CF::D_COLS, v);
-        tmem_ld_wait();
+        // two halves of 16 channels: [hi.hi + lo.hi] and [hi.lo] accumulator columns are summed on the way (keeps the live
+        // registers at 32 + the 32 accumulators; loading both 32-column pieces at once spilled)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 wv = *reinterpret_cast<const float4*>(wsm + 16 * j);
-          acc[4 * j + 0] = fmaf(wv.x, __uint_as_float(v[4 * j + 0]), acc[4 * j + 0]);
-          acc[4 * j + 1] = fmaf(wv.y, __uint_as_float(v[4 * j + 1]), acc[4 * j + 1]);
-          acc[4 * j + 2] = fmaf(wv.z, __uint_as_float(v[4 * j + 2]), acc[4 * j + 2]);
-          acc[4 * j + 3] = fmaf(wv.w, __uint_as_float(v[4 * j + 3]), acc[4 * j + 3]);
+        for (int hf = 0; hf < 2; ++hf) {
+          uint32_t v[16], v2[16];
+          tmem_ld_32x32b_x16(taddr0 + s * CF::D_COLS + hf * 16, v);
+          tmem_ld_32x32b_x16(taddr0 + s * CF::D_COLS + TU_C + hf * 16, v2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 wv = *reinterpret_cast<const float4*>(wsm + 64 * hf + 16 * j);
+            acc[16 * hf + 4 * j + 0] = fmaf(wv.x, __uint_as_float(v[4 * j + 0]) + __uint_as_float(v2[4 * j + 0]), acc[16 * hf + 4 * j + 0]);
+            acc[16 * hf + 4 * j + 1] = fmaf(wv.y, __uint_as_float(v[4 * j + 1]) + __uint_as_float(v2[4 * j + 1]), acc[16 * hf + 4 * j + 1]);
+            acc[16 * hf + 4 * j + 2] = fmaf(wv.z, __uint_as_float(v[4 * j + 2]) + __uint_as_float(v2[4 * j + 2]), acc[16 * hf + 4 * j + 2]);
+            acc[16 * hf + 4 * j + 3] = fmaf(wv.w, __uint_as_float(v[4 * j + 3]) + __uint_as_float(v2[4 * j + 3]), acc[16 * hf + 4 * j + 3]);
+          }
         }
         tc_fence_before_sync();
-        mbar_arrive(&slot_free[s]);
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&slot_free[s]);
+          if (e % TU_WE == TU_WE - 1 || e == e_hi - 1) mbar_arrive(&w_free[wb]);   // last use of the group in this CTA
+        }
       }
       // end of node n: rows without edges store zeros.  thread = row -> (transpose tile) -> 8 lanes per 128-byte row
+      tw.start();
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         *reinterpret_cast<float4*>(stg + lane * TU_STG_LD + 4 * j) =
@@ -195,6 +249,11 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
           __stcs(reinterpret_cast<float4*>(mn + orow * TU_C) + q, *reinterpret_cast<const float4*>(stg + r * TU_STG_LD + 4 * q));
       }
       __syncwarp();
+      tw.stop(pw2);
+    }
+    tt.stop(ptot);
+    if (PROF && warp == 0 && lane == 0) {
+      prof[4] = pw0; prof[5] = pw1; prof[6] = pw2; prof[7] = ptot; prof[10] = n_e; prof[11] = (unsigned long long)(n_hi - n_lo);
     }
   } else if (warp < CF::MMA_WARP) {
     // ======================================================= fill: A = G_e^T (sparse scatter), B = x[sender]^T
@@ -223,24 +282,32 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
       for (int c = 0; c < 4; ++c) xv[c] = c < xcnt ? __ldg(h + ((int64_t)snd * DIN + xi0 + c) * TU_C + lane) : 0.f;
     };
     auto load_y = [&](int e) { return lane < ystride ? __ldg(Y + (int64_t)e * ystride + lane) : 0.f; };
-    float yv = 0.f, xv[4] = {0.f, 0.f, 0.f, 0.f};
-    int s_next = 0;
+    // register prefetch ring, two edges deep (the sender rows come from L2 / HBM: ~1-2 edge periods of latency)
+    auto snd_at = [&](uint32_t i) { return i < n_e ? __ldg(sender + e_lo + i) : 0; };
+    float yv = 0.f, xv[4] = {0.f, 0.f, 0.f, 0.f}, y1v = 0.f, x1v[4] = {0.f, 0.f, 0.f, 0.f};
+    int s2 = snd_at(2), s3 = snd_at(3);
     if (n_e > 0) {
       yv = load_y(e_lo);
-      load_x(__ldg(sender + e_lo), xv);
-      s_next = n_e > 1 ? __ldg(sender + e_lo + 1) : 0;
+      load_x(snd_at(0), xv);
     }
+    if (n_e > 1) {
+      y1v = load_y(e_lo + 1);
+      load_x(snd_at(1), x1v);
+    }
+    tt.start();
     for (uint32_t it = 0; it < n_e; ++it) {
       const uint32_t s = it % S, ph = (it / S) & 1;
-      // prefetch the next edge's inputs before blocking on the slot
-      float yn = 0.f, xn[4] = {0.f, 0.f, 0.f, 0.f};
-      int s_next2 = 0;
-      if (it + 1 < n_e) {
-        yn = load_y(e_lo + (int)it + 1);
-        load_x(s_next, xn);
-        s_next2 = it + 2 < n_e ? __ldg(sender + e_lo + it + 2) : 0;
+      // issue the loads of edge it + 2 before blocking on the slot
+      float y2v = 0.f, x2v[4] = {0.f, 0.f, 0.f, 0.f};
+      if (it + 2 < n_e) {
+        y2v = load_y(e_lo + (int)it + 2);
+        load_x(s2, x2v);
       }
-      tu_wait<32>(&slot_free[s], ph ^ 1);
+      s2 = s3;
+      s3 = snd_at(it + 4);
+      tw.start();
+      tu_wait<0>(&slot_free[s], ph ^ 1);
+      tw.stop(pw0);
       uint8_t* const sl = slots + (size_t)s * CF::SLOT_BYTES;
 #pragma unroll
       for (int qi = 0; qi < I::NIT; ++qi) {
@@ -256,19 +323,27 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
         hi.x = tu_rna(xv[0]); hi.y = tu_rna(xv[1]); hi.z = tu_rna(xv[2]); hi.w = tu_rna(xv[3]);
         lo.x = xv[0] - hi.x; lo.y = xv[1] - hi.y; lo.z = xv[2] - hi.z; lo.w = xv[3] - hi.w;
         *reinterpret_cast<float4*>(sl + b_off) = hi;
-        *reinterpret_cast<float4*>(sl + b_off + CF::B_TERM) = lo;
+        *reinterpret_cast<float4*>(sl + b_off + CF::B_LO) = lo;
       }
       fence_proxy_async_smem();
-      mbar_arrive(&filled[s]);
-      yv = yn;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&filled[s]);
+      yv = y1v;
+      y1v = y2v;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) xv[c] = xn[c];
-      s_next = s_next2;
+      for (int c = 0; c < 4; ++c) {
+        xv[c] = x1v[c];
+        x1v[c] = x2v[c];
+      }
+    }
+    tt.stop(ptot);
+    if (PROF && fw == 0 && lane == 0) {
+      prof[0] = pw0; prof[1] = ptot;
     }
   } else if (warp == CF::MMA_WARP) {
     // ======================================================= MMA issuer (one lane)
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_tf32(128, TU_C);
+      constexpr uint32_t idesc = make_idesc_tf32(128, TU_C), idesc2 = make_idesc_tf32(128, 2 * TU_C);
       const uint32_t desc_hi = (128u >> 4) | (1u << 14);   // SBO = 128 B, descriptor version 1
       auto desc = [desc_hi](uint32_t lo) {
         uint64_t dd;
@@ -277,39 +352,50 @@ k_tp_umma(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
       };
       const uint32_t a_lo0 = ((smem_u32(slots) >> 4) & 0x3FFFu) | (((uint32_t)EEG_TPU_A_LBO >> 4) << 16);
       const uint32_t b_lo0 = (((smem_u32(slots) + CF::A_BYTES) >> 4) & 0x3FFFu) | ((TU_B_LBO >> 4) << 16);
+      tt.start();
       for (uint32_t it = 0; it < n_e; ++it) {
         const uint32_t s = it % S, ph = (it / S) & 1;
+        tw.start();
         tu_wait<0>(&filled[s], ph);
+        tw.stop(pw0);
         tc_fence_after_sync();
         const uint32_t so = s * (CF::SLOT_BYTES >> 4);
 #pragma unroll
         for (int t = 0; t < NT; ++t) {
-          const uint32_t dcol = tmem_base + s * CF::D_COLS + t * TU_C;
+          const uint32_t dcol = tmem_base + s * CF::D_COLS + t * 2 * TU_C;
 #pragma unroll
           for (int ks = 0; ks < CF::KT / 8; ++ks) {
             const uint32_t ad = a_lo0 + so + ((t * CF::A_TILE + ks * 2 * EEG_TPU_A_LBO) >> 4);
             const uint32_t bd = b_lo0 + so + ((t * CF::B_TILE + ks * 2 * TU_B_LBO) >> 4);
-            mma_tf32(dcol, desc(ad), desc(bd), idesc, ks ? 1u : 0u);                       // A_hi x B_hi
-            mma_tf32(dcol, desc(ad + (CF::A_TERM >> 4)), desc(bd), idesc, 1u);             // A_lo x B_hi
-            mma_tf32(dcol, desc(ad), desc(bd + (CF::B_TERM >> 4)), idesc, 1u);             // A_hi x B_lo
+            mma_tf32(dcol, desc(ad), desc(bd), idesc2, ks ? 1u : 0u);                      // A_hi x [B_hi | B_lo]  (N = 64)
+            mma_tf32(dcol, desc(ad + (CF::A_TERM >> 4)), desc(bd), idesc, 1u);             // A_lo x B_hi -> first half
           }
         }
         mma_commit(&d_full[s]);
       }
+      tt.stop(ptot);
+      if (PROF) { prof[2] = pw0; prof[3] = ptot; }
     }
   } else {
-    // ======================================================= weight loader (one lane): 128 B per path by the TMA engine
-    if (lane == 0) {
-      for (uint32_t it = 0; it < n_e; ++it) {
-        const uint32_t s = it % S, ph = (it / S) & 1;
-        tu_wait<64>(&slot_free[s], ph ^ 1);
-        uint8_t* const wsm = slots + (size_t)s * CF::SLOT_BYTES + CF::A_BYTES + CF::B_BYTES;
-        mbar_arrive_expect_tx(&filled[s], I::NPATHS * 128);
-        const float* src = w_t + (int64_t)(e_lo + it) * TU_C;
-#pragma unroll 6
-        for (int p = 0; p < I::NPATHS; ++p) bulk_g2s(wsm + p * TU_W_PITCH, src + (int64_t)p * E * TU_C, 128, &filled[s]);
+    // ======================================================= weight loader: lane l copies paths l, l + 32, ...
+    tt.start();
+    for (uint32_t k = 0; k < n_wg; ++k) {
+      const int wb = (int)(k % TU_WG);
+      const int64_t e0 = (int64_t)(wg0 + (int)k) * TU_WE;
+      const uint32_t bytes = (uint32_t)((E - e0 < TU_WE ? E - e0 : TU_WE) * 128);
+      if (lane == 0) {
+        tw.start();
+        tu_wait<64>(&w_free[wb], ((k / TU_WG) & 1) ^ 1);
+        tw.stop(pw0);
+        mbar_arrive_expect_tx(&w_full[wb], I::NPATHS * bytes);
       }
+      __syncwarp();
+      uint8_t* const wsm = wbufs + (size_t)wb * CF::W_BYTES;
+      for (int p = lane; p < I::NPATHS; p += 32)
+        bulk_g2s(wsm + p * TU_W_PITCH, w_t + ((int64_t)p * E + e0) * TU_C, bytes, &w_full[wb]);
     }
+    tt.stop(ptot);
+    if (PROF && lane == 0) { prof[8] = pw0; prof[9] = ptot; }
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -324,7 +410,8 @@ int launch_tp_umma(const float* h, const float* Y, int ystride, const float* w_t
   static EegDevFlags attr_dev;
   bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k_tp_umma<LIN, LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(k_tp_umma<LIN, LMAX, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tp_umma<LIN, LMAX, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
     if (e != cudaSuccess) {
       eeg_set_error("eeg_tp_scatter_fwd (tcgen05): cannot opt in to %u B shared memory: %s", CF::SMEM_BYTES, cudaGetErrorString(e));
       return 2;
@@ -336,12 +423,24 @@ int launch_tp_umma(const float* h, const float* Y, int ystride, const float* w_t
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = EEG_NUM_SMS;
   int64_t grid = sms;
   if (grid > N) grid = N;
-  k_tp_umma<LIN, LMAX><<<(unsigned)grid, CF::THREADS, CF::SMEM_BYTES, s>>>(h, Y, ystride, w_t, E, sender, row_ptr, inv_norm, M, N);
+  static const bool prof = getenv("EEG_TP_PROF") && atoi(getenv("EEG_TP_PROF")) != 0;
+  if (prof) k_tp_umma<LIN, LMAX, true><<<(unsigned)grid, CF::THREADS, CF::SMEM_BYTES, s>>>(h, Y, ystride, w_t, E, sender, row_ptr, inv_norm, M, N);
+  else k_tp_umma<LIN, LMAX, false><<<(unsigned)grid, CF::THREADS, CF::SMEM_BYTES, s>>>(h, Y, ystride, w_t, E, sender, row_ptr, inv_norm, M, N);
   EEG_CHECK_LAUNCH("eeg_tp_scatter_fwd (tcgen05)");
   return 0;
 }
 
 }  // namespace
+
+// Debug: copies the per-CTA stall counters of the last EEG_TP_PROF=1 launch (EEG_NUM_SMS x 16 uint64) to host memory.
+extern "C" int eeg_tp_umma_prof_read(unsigned long long* host_out) {
+  cudaError_t e = cudaMemcpyFromSymbol(host_out, eeg_tpu_prof, sizeof(unsigned long long) * EEG_NUM_SMS * 16);
+  if (e != cudaSuccess) {
+    eeg_set_error("eeg_tp_umma_prof_read: %s", cudaGetErrorString(e));
+    return 2;
+  }
+  return 0;
+}
 
 // Returns 0 when launched, -1 when the shape is outside this kernel (the caller then runs the CUDA-core kernel).
 int eeg_tp_umma_launch(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t, int64_t E,

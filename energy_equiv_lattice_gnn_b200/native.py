@@ -23,6 +23,7 @@ SYMBOLS = [
     "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
     "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
+    "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd",
 ]
 
 
@@ -264,10 +265,17 @@ def radial_mlp(f, W0, b0, bh, n_hidden, img, n_out):
     return w_t
 
 
-def tp_scatter(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes):
+def tp_scatter(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes, umma: bool = False):
+    """umma=True calls the tensor-core variant (eeg_tp_scatter_umma_fwd: C = 32, lmax_in = lmax only)."""
     M = torch.empty(n_nodes, rows_total * Cch, dtype=f32, device=h.device)
     E = w_t.shape[1]
-    _begin("eeg_tp_scatter_fwd")
+    name = "eeg_tp_scatter_umma_fwd" if umma else "eeg_tp_scatter_fwd"
+    _begin(name)
+    if umma:
+        _check(lib().eeg_tp_scatter_umma_fwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]),
+                                             _p(w_t, f32), C.c_int64(E), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm),
+                                             _p(M), C.c_int64(n_nodes), _stream()), name)
+        return M
     _check(lib().eeg_tp_scatter_fwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]),
                                     _p(w_t, f32), C.c_int64(E), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm),
                                     _p(M), C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_fwd")
@@ -458,6 +466,35 @@ def scale_rows_inv_degree(x, row_ptr):
     _begin("eeg_scale_rows_inv_degree")
     _check(lib().eeg_scale_rows_inv_degree(_p(x, f32), _p(row_ptr, i32), C.c_int64(x.shape[0]), C.c_int64(x.numel() // max(x.shape[0], 1)),
                                            _stream()), "eeg_scale_rows_inv_degree")
+
+
+def collate_gather(ds_pos, ds_nattr, ds_snd, ds_rcv, ds_shifts, ds_eattr, meta, G: int, N: int, E: int, graph_rows=None, graph_idx=None):
+    """meta: int64 device [4, G+1] = src_node_off, src_edge_off, out_node_ptr, out_edge_ptr (rows 0-1 use the first G entries).
+    -> (positions, node_attrs [N,1], edge_index [2,E], shifts, edge_attr [E,1], batch, gathered graph rows or None)"""
+    dev = ds_pos.device
+    o_pos = torch.empty(N, 3, dtype=f32, device=dev)
+    o_na = torch.empty(N, 1, dtype=f32, device=dev)
+    o_ei = torch.empty(2, E, dtype=i64, device=dev)
+    o_sh = torch.empty(E, 3, dtype=f32, device=dev)
+    o_ea = torch.empty(E, 1, dtype=f32, device=dev)
+    o_b = torch.empty(N, dtype=i64, device=dev)
+    width = 0 if graph_rows is None else graph_rows.shape[1]
+    o_g = torch.empty(G, width, dtype=f32, device=dev) if graph_rows is not None else None
+    _begin("eeg_collate_gather")
+    _check(lib().eeg_collate_gather(_p(ds_pos, f32), _p(ds_nattr, f32), _p(ds_snd, i32), _p(ds_rcv, i32), _p(ds_shifts, f32),
+                                    _p(ds_eattr, f32), _p(meta[0], i64), _p(meta[1], i64), _p(meta[2], i64), _p(meta[3], i64),
+                                    C.c_int64(G), C.c_int64(N), C.c_int64(E), _p(o_pos), _p(o_na), _p(o_ei), _p(o_sh), _p(o_ea), _p(o_b),
+                                    _p(graph_rows, f32) if graph_rows is not None else C.c_void_p(0),
+                                    _p(graph_idx, i64) if graph_idx is not None else C.c_void_p(0), C.c_int64(width), _p(o_g), _stream()),
+           "eeg_collate_gather")
+    return o_pos, o_na, o_ei, o_sh, o_ea, o_b, o_g
+
+
+def rand_rotations(seed: int, offset: int, G: int, device) -> torch.Tensor:
+    Q = torch.empty(G, 3, 3, dtype=f32, device=device)
+    _begin("eeg_rand_rotations")
+    _check(lib().eeg_rand_rotations(C.c_uint64(seed & (2 ** 64 - 1)), C.c_uint64(offset), C.c_int64(G), _p(Q), _stream()), "eeg_rand_rotations")
+    return Q
 
 
 # ---- device guard -----------------------------------------------------------------------------------------------------

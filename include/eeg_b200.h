@@ -94,6 +94,11 @@ int eeg_radial_mlp_fwd(const float* f, int n_in, const float* W0, const float* b
 int eeg_tp_scatter_fwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
                        int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, float* M,
                        int64_t N, void* stream);
+/* Same contract on the tensor cores (csrc/eeg_tp_umma.cu: one [230 x 25] x [25 x 32] 3xTF32 tcgen05 product per edge, TMEM
+ * accumulators, TMA weight stream); C = 32 and lmax_in = lmax in {3, 4} only, otherwise returns 1. */
+int eeg_tp_scatter_umma_fwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
+                            int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, float* M,
+                            int64_t N, void* stream);
 
 /* ---- symmetric contraction (product basis): gnn/mace.py:112-277
  * eeg_sc_coefficients: T[C, n_coef] (channel-major) = (A_csr @ Wflat[n_wrows, C])^T   (A = symmetrised U tensors, built by the host)
@@ -197,6 +202,23 @@ int eeg_scale_rows_inv_degree(float* x, const int32_t* row_ptr, int64_t N, int64
 int eeg_rotate_vec3(const float* Q, const int64_t* graph_of, const int64_t* via, const float* in, float* out, int64_t n,
                     void* stream);
 int eeg_rotate_cart4_to_mandel(const float* Q, const float* C4, float* out, int64_t G, void* stream);
+
+/* ---- batch construction on the device (scripts/train_main.py:67-78: PyG DataLoader -> Batch.from_data_list).
+ * The dataset lives in HBM in flat form (flatdata.FlatDataset): node arrays pos [SN,3], node_attrs [SN]; edge arrays
+ * edge_snd / edge_rcv int32 [SE] (LOCAL node ids of the lattice), shifts [SE,3], edge_attr [SE].  A batch of G lattices is
+ * described by four int64 device arrays: src_node_off / src_edge_off [G] (first node / edge of each chosen lattice in the
+ * dataset) and out_node_ptr / out_edge_ptr [G+1] (exclusive cumsum of their node / edge counts; [G] = N / E).
+ * Writes the PyG batch: positions, node_attrs, edge_index int64 [2,E] (local id + node offset of the graph), shifts, edge_attr,
+ * batch int64 [N]; optionally gathers per-lattice rows (targets): o_graph_rows[g, :] = graph_rows[graph_idx[g], :]. */
+int eeg_collate_gather(const float* pos, const float* node_attrs, const int32_t* edge_snd, const int32_t* edge_rcv,
+                       const float* shifts, const float* edge_attr, const int64_t* src_node_off, const int64_t* src_edge_off,
+                       const int64_t* out_node_ptr, const int64_t* out_edge_ptr, int64_t G, int64_t N, int64_t E, float* o_pos,
+                       float* o_node_attrs, int64_t* o_edge_index, float* o_shifts, float* o_edge_attr, int64_t* o_batch,
+                       const float* graph_rows /*[L,width] or NULL*/, const int64_t* graph_idx /*[G]*/, int64_t graph_width,
+                       float* o_graph_rows /*[G,width]*/, void* stream);
+/* G proper rotations drawn like e3nn o3.rand_matrix() (scripts/train_utils.py:121): alpha, gamma ~ U[0,2pi), cos(beta) ~ U[-1,1],
+ * Q = Ry(alpha) Rx(beta) Ry(gamma); counter-based generator: lattice g of the call uses counters 3*(offset+g) .. +2. */
+int eeg_rand_rotations(uint64_t seed, uint64_t offset, int64_t G, float* Q /*[G,3,3]*/, void* stream);
 
 /* ---- validation / test metrics (scripts/train_utils.py:66-89 validation_step, :149-172 obtain_errors; SURVEY.md 8(f)
  * rank 3).  pred, target: Mandel [G,6,6]; directions: [P,3] unit vectors.  per_lattice [G,4] = (mean squared error and mean

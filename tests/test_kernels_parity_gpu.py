@@ -39,8 +39,8 @@ def tp_reference(plan, h, Y, w_t, snd, row_ptr, inv_norm, C):
     return M * inv_norm
 
 
-@pytest.mark.parametrize("lmax,C", [(4, 32), (3, 32), (3, 64)])
-def test_tp_scatter_op(cuda_device, lmax, C):
+@pytest.mark.parametrize("lmax,C,umma", [(4, 32, False), (4, 32, True), (3, 32, False), (3, 32, True), (3, 64, False)])
+def test_tp_scatter_op(cuda_device, lmax, C, umma):
     plan = tb.tp_plan(lmax, lmax, lmax)
     g = torch.Generator().manual_seed(100 + lmax + C)
     N = 301
@@ -63,9 +63,9 @@ def test_tp_scatter_op(cuda_device, lmax, C):
     want = tp_reference(plan, h.reshape(N, D, C), Y, w, snd, row_ptr, 0.25, C)
     d = cuda_device
     got = nv.tp_scatter(lmax, lmax, C, h.reshape(N, D * C).to(d).contiguous(), Y.to(d), w_t.to(d), snd.to(d), row_ptr.to(d), 0.25,
-                        plan["rows_total"], N)
+                        plan["rows_total"], N, umma=umma)
     got2 = nv.tp_scatter(lmax, lmax, C, h.reshape(N, D * C).to(d).contiguous(), Y.to(d), w_t.to(d), snd.to(d), row_ptr.to(d), 0.25,
-                         plan["rows_total"], N)
+                         plan["rows_total"], N, umma=umma)
     torch.cuda.synchronize()
     assert torch.equal(got, got2), "tensor-product scatter is not bitwise repeatable"
     got = got.reshape(N, plan["rows_total"], C)
