@@ -34,6 +34,13 @@ def forward_with_grad(model, batch) -> torch.Tensor:
     return _Forward.apply(model, batch, *list(model.parameters()))
 
 
+def _sender_csr(sv, N):
+    """CSR of the batch's (receiver-sorted) edges by sender, built once per backward and shared by the layers."""
+    if "snd_csr" not in sv:
+        sv["snd_csr"] = nv.sender_csr(sv["snd"], N)
+    return sv["snd_csr"]
+
+
 def _static(model, name, build):
     hit = model._cache.get(name)
     if hit is None:
@@ -145,7 +152,7 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         # tensor product + scatter
         nv.set_tag(f'bwd.L{i}.tp_scatter')
         dw, dhup = nv.tp_scatter_bwd(0 if i == 0 else lmax, lmax, C, sv["hup"][i], sv["Y"], sv["w"][i], sv["snd"], sv["row_ptr"],
-                                     1.0, dM, len(plan["paths"]), N)
+                                     1.0, dM, len(plan["paths"]), N, snd_csr=_sender_csr(sv, N))
         # radial MLP
         lins = [m for m in inter.conv_tp_weights if isinstance(m, torch.nn.Linear)]
         nv.set_tag(f'bwd.L{i}.radial_mlp')

@@ -26,8 +26,12 @@ struct WgParams {
   int n_blocks, in_stride, out_stride, transB;
 };
 
+// ws != nullptr: deterministic mode - the row slice `cta / tiles` of a tile writes its partial sums to
+// ws[slice * ws_stride + element] (bias partials behind the weights at n_weights + column) and k_wgrad_reduce adds the
+// slices in order; ws == nullptr: one atomicAdd per element and slice (order depends on scheduling).
 __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dW,
-                                                      float* __restrict__ dbias, int64_t N, WgParams P) {
+                                                      float* __restrict__ dbias, int64_t N, WgParams P, float* __restrict__ ws,
+                                                      int64_t ws_stride, int64_t n_weights) {
   __shared__ __align__(16) float Xs[32][36];
   __shared__ __align__(16) float Ys[32][36];
   int cta = blockIdx.x, bi = 0;
@@ -74,24 +78,50 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
     }
     __syncthreads();
   }
-  float* Wb = dW + d.w_off;
+  float* const wsl = ws ? ws + (int64_t)(cta / tiles) * ws_stride : nullptr;
+  float* Wb = (ws ? wsl : dW) + d.w_off;
 #pragma unroll
   for (int i = 0; i < 2; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int k = kt * 32 + 2 * tk + i, n = nt * 32 + 4 * tn + j;
-      if (k < d.k && n < d.nout) atomicAdd(Wb + (P.transB ? (int64_t)n * d.k + k : (int64_t)k * d.nout + n), acc[i][j] * d.scale);
+      if (k < d.k && n < d.nout) {
+        float* dst = Wb + (P.transB ? (int64_t)n * d.k + k : (int64_t)k * d.nout + n);
+        if (ws) *dst = acc[i][j] * d.scale;
+        else atomicAdd(dst, acc[i][j] * d.scale);
+      }
     }
   if (want_bias)
 #pragma unroll
     for (int j = 0; j < 4; ++j)
-      if (nt * 32 + 4 * tn + j < d.nout) atomicAdd(dbias + nt * 32 + 4 * tn + j, bsum[j]);
+      if (nt * 32 + 4 * tn + j < d.nout) {
+        if (ws) wsl[n_weights + nt * 32 + 4 * tn + j] = bsum[j];
+        else atomicAdd(dbias + nt * 32 + 4 * tn + j, bsum[j]);
+      }
+}
+
+// dW[i] += sum over the row slices of i's block, in slice order (fixed order: bitwise repeatable)
+__global__ void k_wgrad_reduce(const float* __restrict__ ws, int64_t ws_stride, int64_t n_weights, int bias_cols, float* __restrict__ dW,
+                               float* __restrict__ dbias, int64_t N, WgParams P) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n_weights + bias_cols) return;
+  int b = -1;
+  if (i >= n_weights) b = 0;
+  else
+    for (int q = 0; q < P.n_blocks; ++q)
+      if (P.b[q].k > 0 && P.b[q].nout > 0 && i >= P.b[q].w_off && i < P.b[q].w_off + (int64_t)P.b[q].k * P.b[q].nout) b = q;
+  if (b < 0) return;
+  const int64_t slices = (N * P.b[b].rows + WG_ROWS - 1) / WG_ROWS;
+  float s = 0.f;
+  for (int64_t sl = 0; sl < slices; ++sl) s += ws[sl * ws_stride + i];
+  if (i >= n_weights) dbias[i - n_weights] += s;
+  else dW[i] += s;
 }
 
 // ------------------------------------------------------------------------------------------------ column sums
 // block = 32 columns x 8 row lanes; a CTA sums rows_per_cta rows (fixed order inside the CTA), one atomicAdd per column
 __global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ x, int64_t R, int ld, int cols, const float* __restrict__ a,
-                                                float* __restrict__ out, int rows_per_cta) {
+                                                float* __restrict__ out, int rows_per_cta, float* __restrict__ ws) {
   __shared__ float part[8][33];
   const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
   const int c = blockIdx.y * 32 + cl;
@@ -105,8 +135,16 @@ __global__ void __launch_bounds__(256) k_colsum(const float* __restrict__ x, int
     float t = 0.f;
 #pragma unroll
     for (int q = 0; q < 8; ++q) t += part[q][cl];
-    atomicAdd(out + c, t);
+    if (ws) ws[(int64_t)blockIdx.x * cols + c] = t;   // deterministic mode: k_colsum_reduce adds the CTA partials in order
+    else atomicAdd(out + c, t);
   }
+}
+__global__ void k_colsum_reduce(const float* __restrict__ ws, int64_t parts, int cols, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (int64_t p = 0; p < parts; ++p) s += ws[p * cols + c];
+  out[c] += s;
 }
 
 __global__ void k_silu_fwd(const float* __restrict__ a, float* __restrict__ s, int64_t n) {
@@ -346,7 +384,8 @@ void fill_tail(TailBwdParams& T, const EegLayout* lo, const int32_t* host_qmul, 
 
 extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
                                       const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
-                                      const int32_t* k_override, float* dW, float* dbias, int64_t N, void* stream) {
+                                      const int32_t* k_override, float* dW, float* dbias, int64_t N, int64_t n_weights, float* ws,
+                                      int64_t ws_floats, void* stream) {
   EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_wgrad: layout mismatch");
   if (N == 0) return 0;
   WgParams P;
@@ -378,17 +417,50 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
     EEG_REQUIRE(ctas < (1LL << 31), "eeg_block_linear_wgrad: too many tiles");
   }
   if (ctas == 0) return 0;
-  k_linear_wgrad<<<(unsigned)ctas, 128, 0, (cudaStream_t)stream>>>(x, dy, dW, dbias, N, P);
+  const int bias_cols = dbias ? P.b[0].nout : 0;
+  const int64_t stride = n_weights + bias_cols;
+  if (ws != nullptr) {
+    int64_t slices = 0;
+    for (int b = 0; b < P.n_blocks; ++b) {
+      const int64_t sl = (N * P.b[b].rows + WG_ROWS - 1) / WG_ROWS;
+      if (P.b[b].k > 0 && P.b[b].nout > 0 && sl > slices) slices = sl;
+      EEG_REQUIRE(P.b[b].k == 0 || P.b[b].nout == 0 || P.b[b].w_off + (int64_t)P.b[b].k * P.b[b].nout <= n_weights,
+                  "eeg_block_linear_wgrad: block %d exceeds n_weights", b);
+    }
+    EEG_REQUIRE(ws_floats >= slices * stride, "eeg_block_linear_wgrad: workspace too small (%lld < %lld floats)", (long long)ws_floats,
+                (long long)(slices * stride));
+  }
+  k_linear_wgrad<<<(unsigned)ctas, 128, 0, (cudaStream_t)stream>>>(x, dy, dW, dbias, N, P, ws, stride, n_weights);
   EEG_CHECK_LAUNCH("eeg_block_linear_wgrad");
+  if (ws != nullptr) {
+    k_wgrad_reduce<<<(unsigned)((stride + 255) / 256), 256, 0, (cudaStream_t)stream>>>(ws, stride, n_weights, bias_cols, dW, dbias, N, P);
+    EEG_CHECK_LAUNCH("eeg_block_linear_wgrad (reduce)");
+  }
   return 0;
 }
 
-extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream) {
+// floats of workspace eeg_block_linear_wgrad needs in deterministic mode
+extern "C" int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, int64_t n_weights, int bias_cols, int64_t N) {
+  int64_t slices = 0;
+  for (int b = 0; lin && b < lin->n_blocks; ++b) {
+    const int64_t sl = (N * lin->rows[b] + WG_ROWS - 1) / WG_ROWS;
+    if (sl > slices) slices = sl;
+  }
+  return slices * (n_weights + bias_cols);
+}
+
+extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,
+                          void* stream) {
   if (R == 0 || cols == 0) return 0;
   const int rows_per_cta = 256;
   dim3 grid((unsigned)((R + rows_per_cta - 1) / rows_per_cta), (unsigned)((cols + 31) / 32));
-  k_colsum<<<grid, 256, 0, (cudaStream_t)stream>>>(x, R, ld, cols, row_scale, out, rows_per_cta);
+  EEG_REQUIRE(ws == nullptr || ws_floats >= (int64_t)grid.x * cols, "eeg_colsum: workspace too small (need ceil(R/256) * cols floats)");
+  k_colsum<<<grid, 256, 0, (cudaStream_t)stream>>>(x, R, ld, cols, row_scale, out, rows_per_cta, ws);
   EEG_CHECK_LAUNCH("eeg_colsum");
+  if (ws != nullptr) {
+    k_colsum_reduce<<<(unsigned)((cols + 127) / 128), 128, 0, (cudaStream_t)stream>>>(ws, grid.x, cols, out);
+    EEG_CHECK_LAUNCH("eeg_colsum (reduce)");
+  }
   return 0;
 }
 
@@ -448,17 +520,19 @@ extern "C" int eeg_pool_tail_bwd(const float* o, const EegLayout* lo, const int3
 // torch.optim.AdamW(amsgrad) + Lightning gradient_clip_val (scripts/train_utils.py:38-44, scripts/train_main.py:89-92) on
 // one flat fp32 buffer: g <- grad_scale * g (e.g. 1/world after an all-reduce sum), clipped by max_norm / (|g| + 1e-6).
 namespace {
-__global__ void k_sumsq(const float* __restrict__ x, int64_t n, float* __restrict__ out) {
+// ONE CTA, fixed summation order (the flat gradient is < 1 MB: a multi-CTA atomicAdd made the clip factor, and with it
+// every parameter, depend on the scheduling order)
+__global__ void __launch_bounds__(1024) k_sumsq(const float* __restrict__ x, int64_t n, float* __restrict__ out) {
   float s = 0.f;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) s = fmaf(x[i], x[i], s);
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) s = fmaf(x[i], x[i], s);
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  __shared__ float ws[8];
+  __shared__ float ws[32];
   if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
   __syncthreads();
   if (threadIdx.x == 0) {
     float t = 0.f;
     for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += ws[w];
-    atomicAdd(out, t);
+    out[0] += t;
   }
 }
 __global__ void k_adamw(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
@@ -488,8 +562,7 @@ __global__ void k_adamw(float* __restrict__ p, const float* __restrict__ g, floa
 
 extern "C" int eeg_sumsq(const float* x, int64_t n, float* out, void* stream) {
   if (n == 0) return 0;
-  const unsigned grid = (unsigned)((n + 255) / 256 < 1024 ? (n + 255) / 256 : 1024);
-  k_sumsq<<<grid, 256, 0, (cudaStream_t)stream>>>(x, n, out);
+  k_sumsq<<<1, 1024, 0, (cudaStream_t)stream>>>(x, n, out);
   EEG_CHECK_LAUNCH("eeg_sumsq");
   return 0;
 }

@@ -1,6 +1,8 @@
 // Backward of the channelwise tensor-product message + scatter (gnn/blocks.py:591-597).
 //   dw[e, p*C + c]      = inv_norm * sum_k dM[recv(e), row(p,k), c] * t_{p,k}(h'[send(e)], Y_e)          (edge-major, CSR order)
-//   dh'[send(e), i, c] += inv_norm * sum_p w[e,p,c] sum_k G_p[i,k](Y_e) dM[recv(e), row(p,k), c]          (atomic adds)
+//   dx[e, i, c]         = inv_norm * sum_p w[e,p,c] sum_k G_p[i,k](Y_e) dM[recv(e), row(p,k), c]          (edge-major, CSR order)
+//   dh'[s, i, c]        = sum_{e : send(e) = s} dx[e, i, c]   by eeg_segment_sum_rows over the SENDER-sorted CSR (fixed order: the
+//                         gradient is bitwise repeatable; the first version used atomicAdd into the sender rows)
 // One warp per run of 16 receiver rows (contiguous CSR edges), lane = channel; per edge the lane-uniform matrices
 // G_p[i,k] = sum_j C_p[i,j,k] Y_j are staged once per warp in shared memory (the forward's table), then a generated
 // straight-line function (tools/gen_kernels.py: gen_tp2_bwd) evaluates every path.
@@ -83,7 +85,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__
         for (int p = 0; p < I::NPATHS; ++p) dwp[(int64_t)p * C] *= inv_norm;
       }
 #pragma unroll
-      for (int d = 0; d < DIN; ++d) atomicAdd(dh + ((int64_t)s * DIN + d) * C + c, dx[d] * inv_norm);
+      for (int d = 0; d < DIN; ++d) __stcs(dh + ((int64_t)e * DIN + d) * C + c, dx[d] * inv_norm);   // dh = per-edge rows [E, DIN, C]
     }
   }
 }
@@ -109,12 +111,41 @@ int launch_tpb(const float* h, const float* Y, int ystride, const float* w_t, in
   return 0;
 }
 
+// out[n, :] = sum over j in [ptr[n], ptr[n+1]) of in[perm[j], :], one thread per float4 column, rows added in CSR order
+__global__ void __launch_bounds__(256) k_segment_sum_rows(const float4* __restrict__ in, const int32_t* __restrict__ perm,
+                                                          const int32_t* __restrict__ ptr, int64_t N, int w4, float4* __restrict__ out) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= N * w4) return;
+  const int64_t n = i / w4;
+  const int c = (int)(i - n * w4);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int e1 = __ldg(ptr + n + 1);
+  for (int j = __ldg(ptr + n); j < e1; ++j) {
+    const float4 v = __ldcs(in + (int64_t)__ldg(perm + j) * w4 + c);
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  }
+  out[i] = s;
+}
+
 }  // namespace
 
-// dw [E, n_paths*C] (CSR order) is fully written; dh [N, (lmax_in+1)^2, C] must be zero-initialised by the caller.
+extern "C" int eeg_segment_sum_rows(const float* in, const int32_t* perm, const int32_t* ptr, int64_t N, int64_t width, float* out,
+                                    void* stream) {
+  EEG_REQUIRE(width > 0 && width % 4 == 0, "eeg_segment_sum_rows: width must be a positive multiple of 4 (got %lld)", (long long)width);
+  if (N == 0) return 0;
+  const int64_t total = N * (width / 4);
+  k_segment_sum_rows<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float4*>(in), perm, ptr, N, (int)(width / 4), reinterpret_cast<float4*>(out));
+  EEG_CHECK_LAUNCH("eeg_segment_sum_rows");
+  return 0;
+}
+
+// dw [E, n_paths*C] and dx_edge [E, (lmax_in+1)^2 * C] (both in CSR order) are fully written; the sender-side sum of dx_edge
+// is eeg_segment_sum_rows (below) over a CSR of the sender_sorted array.
 extern "C" int eeg_tp_scatter_bwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
                                   int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, const float* dM,
-                                  float* dw, float* dh, int64_t N, void* stream) {
+                                  float* dw, float* dx_edge, int64_t N, void* stream) {
+  float* dh = dx_edge;
   EEG_REQUIRE(C > 0 && C % 32 == 0, "eeg_tp_scatter_bwd: C must be a multiple of 32 (got %d)", C);
   if (N == 0 || E == 0) return 0;
   EEG_REQUIRE(ystride % 4 == 0 && ystride <= 32, "eeg_tp_scatter_bwd: ystride must be a multiple of 4 and <= 32 (got %d)", ystride);

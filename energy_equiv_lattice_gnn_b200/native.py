@@ -23,7 +23,8 @@ SYMBOLS = [
     "eeg_block_linear_wgrad", "eeg_colsum", "eeg_silu_fwd", "eeg_silu_bwd", "eeg_gate_bwd", "eeg_pool_tail_bwd",
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
     "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
-    "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd",
+    "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd", "eeg_segment_sum_rows",
+    "eeg_block_linear_wgrad_ws_floats",
 ]
 
 
@@ -334,9 +335,14 @@ def linear_wgrad(x, lin: EegLayout, dy, lout: EegLayout, w_off, scale, n_weights
     """-> (dW [n_weights], dbias [want_bias] or None); dW_b[u,w] = scale_b sum_rows x[.,u] dy[.,w]."""
     dW = torch.zeros(n_weights, dtype=f32, device=x.device)
     db = torch.zeros(want_bias, dtype=f32, device=x.device) if want_bias else None
+    L = lib()
+    L.eeg_block_linear_wgrad_ws_floats.restype = C.c_int64
+    nws = int(L.eeg_block_linear_wgrad_ws_floats(C.byref(lin), C.c_int64(n_weights), C.c_int(want_bias), C.c_int64(n_rows)))
+    ws = torch.empty(max(nws, 1), dtype=f32, device=x.device)   # deterministic mode: row slices are added in fixed order
     _begin("eeg_block_linear_wgrad")
-    _check(lib().eeg_block_linear_wgrad(_p(x, f32), C.byref(lin), _p(dy, f32), C.byref(lout), _arr(C.c_int64, w_off), _arr(C.c_float, scale, fill=0.0),
-                                        C.c_int(int(transB)), C.c_void_p(0), C.c_void_p(0), _p(dW), _p(db), C.c_int64(n_rows), _stream()),
+    _check(L.eeg_block_linear_wgrad(_p(x, f32), C.byref(lin), _p(dy, f32), C.byref(lout), _arr(C.c_int64, w_off), _arr(C.c_float, scale, fill=0.0),
+                                    C.c_int(int(transB)), C.c_void_p(0), C.c_void_p(0), _p(dW), _p(db), C.c_int64(n_rows),
+                                    C.c_int64(n_weights), _p(ws), C.c_int64(ws.numel()), _stream()),
            "eeg_block_linear_wgrad")
     return dW, db
 
@@ -345,8 +351,10 @@ def colsum(x, row_scale=None):
     """out[c] = sum_r row_scale[r] * x[r, c] for a 2-D contiguous x."""
     R, cols = x.shape
     out = torch.zeros(cols, dtype=f32, device=x.device)
+    ws = torch.empty(((R + 255) // 256) * cols + 1, dtype=f32, device=x.device)
     _begin("eeg_colsum")
-    _check(lib().eeg_colsum(_p(x, f32), C.c_int64(R), C.c_int(cols), C.c_int(cols), _p(row_scale, f32), _p(out), _stream()), "eeg_colsum")
+    _check(lib().eeg_colsum(_p(x, f32), C.c_int64(R), C.c_int(cols), C.c_int(cols), _p(row_scale, f32), _p(out), _p(ws),
+                            C.c_int64(ws.numel()), _stream()), "eeg_colsum")
     return out
 
 
@@ -390,15 +398,31 @@ def pool_tail_bwd(o, lo: EegLayout, gp, Wq, qmul, qscale, bias_len: int, P, posi
     return d_o, dWq, db
 
 
-def tp_scatter_bwd(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, dM, n_paths, n_nodes):
-    """-> (dw [E, n_paths*C] edge-major CSR order, dh [N, (lmax_in+1)^2 * C])"""
+def sender_csr(sender_sorted, n_nodes: int):
+    """CSR of the receiver-sorted edge list by SENDER: (ptr int32 [N+1], perm int32 [E]), stable -> fixed summation order."""
+    E = sender_sorted.shape[0]
+    ei = torch.stack([torch.zeros(E, dtype=i64, device=sender_sorted.device), sender_sorted.to(i64)]).contiguous()
+    return csr_build(ei, n_nodes)
+
+
+def tp_scatter_bwd(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, dM, n_paths, n_nodes, snd_csr=None):
+    """-> (dw [E, n_paths*C] edge-major CSR order, dh [N, (lmax_in+1)^2 * C]).  No atomics: per-edge input gradients are
+    written edge-major and summed per sender by a CSR walk (snd_csr = sender_csr(sender_sorted, N), built here if omitted)."""
     E = w_t.shape[1]
     dw = torch.empty(E, n_paths * Cch, dtype=f32, device=h.device)
-    dh = torch.zeros_like(h)
+    width = h.shape[1]
+    dxe = torch.empty(E, width, dtype=f32, device=h.device)
     _begin("eeg_tp_scatter_bwd")
     _check(lib().eeg_tp_scatter_bwd(C.c_int(lmax_in), C.c_int(lmax), C.c_int(Cch), _p(h, f32), _p(Y, f32), C.c_int(Y.shape[1]), _p(w_t, f32),
-                                    C.c_int64(E), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm), _p(dM, f32), _p(dw), _p(dh),
+                                    C.c_int64(E), _p(sender_sorted, i32), _p(row_ptr, i32), C.c_float(inv_norm), _p(dM, f32), _p(dw), _p(dxe),
                                     C.c_int64(n_nodes), _stream()), "eeg_tp_scatter_bwd")
+    if snd_csr is None:
+        snd_csr = sender_csr(sender_sorted, n_nodes)
+    ptr, perm = snd_csr
+    dh = torch.empty_like(h)
+    _begin("eeg_segment_sum_rows")
+    _check(lib().eeg_segment_sum_rows(_p(dxe, f32), _p(perm, i32), _p(ptr, i32), C.c_int64(n_nodes), C.c_int64(width), _p(dh), _stream()),
+           "eeg_segment_sum_rows")
     return dw, dh
 
 

@@ -129,12 +129,22 @@ int eeg_pool_tail_fwd(const float* o, const EegLayout* lo, const int32_t* graph_
  * ==================================================================================================================== */
 
 /* dW_b[u,w] += scale_b * sum_{n,m} x[n,b,m,u] dy[n,b,m,w]  (transB = 1: stored as dW_b[w,u], torch.nn.Linear layout);
- * dbias[w] += sum_n dy[n,0,0,w] (may be NULL).  in_ld / k_override may be NULL (row stride / K = mul of the layout). */
+ * dbias[w] += sum_n dy[n,0,0,w] (may be NULL).  in_ld / k_override may be NULL (row stride / K = mul of the layout).
+ * n_weights = floats of dW.  ws: workspace of eeg_block_linear_wgrad_ws_floats(lin, n_weights, bias columns, N) floats ->
+ * DETERMINISTIC (row slices are written to ws and added in slice order); ws NULL -> atomicAdd per slice (order varies). */
 int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
                            const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
-                           const int32_t* k_override, float* dW, float* dbias, int64_t N, void* stream);
-/* out[c] += sum_r row_scale[r] * x[r*ld + c]   (row_scale may be NULL = 1): bias / embedding gradients */
-int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream);
+                           const int32_t* k_override, float* dW, float* dbias, int64_t N, int64_t n_weights, float* ws,
+                           int64_t ws_floats, void* stream);
+int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, int64_t n_weights, int bias_cols, int64_t N);
+/* out[c] += sum_r row_scale[r] * x[r*ld + c]   (row_scale may be NULL = 1): bias / embedding gradients.
+ * ws: ceil(R / 256) * cols floats -> deterministic (CTA partials added in order); NULL -> atomicAdd. */
+int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,
+               void* stream);
+/* out[n, :] = sum_{j in [ptr[n], ptr[n+1])} in[perm[j], :]  (rows of `width` floats, width % 4 == 0; fixed order): the
+ * sender-side scatter of the tensor-product backward as a CSR walk instead of atomics. */
+int eeg_segment_sum_rows(const float* in, const int32_t* perm, const int32_t* ptr, int64_t N, int64_t width, float* out,
+                         void* stream);
 /* SiLU of the radial MLP (gnn/blocks.py:538-549): s = silu(a);  da = ds * silu'(a) */
 int eeg_silu_fwd(const float* a, float* s, int64_t n, void* stream);
 int eeg_silu_bwd(const float* a, const float* ds, float* da, int64_t n, void* stream);
@@ -147,10 +157,11 @@ int eeg_pool_tail_bwd(const float* o, const EegLayout* lo, const int32_t* graph_
                       const int32_t* host_qmul, const float* host_qscale, const float* P, int positive, int reduce,
                       const float* A, const float* dC, float* d_o, float* dq_ws, float* pooled_ws, float* dWq, float* dbias,
                       int64_t G, void* stream);
-/* Backward of eeg_tp_scatter_fwd: dw [E, n_paths*C] (edge-major, CSR order; fully written), dh [N,(lmax_in+1)^2,C] += */
+/* Backward of eeg_tp_scatter_fwd: dw [E, n_paths*C] and dx_edge [E,(lmax_in+1)^2*C] (edge-major, CSR order; fully written, no
+ * atomics).  dh[s] = sum of dx_edge over the edges sent by s: eeg_segment_sum_rows with a CSR of sender_sorted. */
 int eeg_tp_scatter_bwd(int lmax_in, int lmax, int C, const float* h, const float* Y, int ystride, const float* w_t,
                        int64_t E, const int32_t* sender_sorted, const int32_t* row_ptr, float inv_norm, const float* dM,
-                       float* dw, float* dh, int64_t N, void* stream);
+                       float* dw, float* dx_edge, int64_t N, void* stream);
 /* Backward of eeg_sym_contract_fwd w.r.t. x (same coefficient table T as the forward) */
 int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, const float* dout, const float* T, float* dx, int64_t N,
                            void* stream);

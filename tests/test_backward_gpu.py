@@ -1,6 +1,7 @@
 """GPU parity of the explicit backward: parameter gradients of the training loss (scripts/train_utils.py:45-64) from
 the CUDA module's `_bwd` kernels vs torch autograd through the fp64 CPU oracle, same weights, same synthetic lattices.
-Tolerance: 2e-4 of the largest entry of each gradient tensor (fp32 accumulation, atomics in the weight-gradient sums)."""
+Tolerance: 5e-5 of the largest entry of each gradient tensor (fp32 arithmetic with fixed-order reductions against fp64
+autograd; the measured worst case is recorded in profiles/)."""
 import pytest
 import torch
 
@@ -9,7 +10,7 @@ from energy_equiv_lattice_gnn_b200.train import relative_mse_loss, random_psd_ta
 from tests.util import batch_to, cuda_model_from, make_pair
 
 pytestmark = pytest.mark.gpu
-GTOL = 2e-4
+GTOL = 5e-5
 
 
 def _grads(lmax_over, n_lat, cuda_device, positive="matrix_power_2"):
@@ -32,9 +33,21 @@ def _grads(lmax_over, n_lat, cuda_device, positive="matrix_power_2"):
                                            (dict(lmax=3, hidden_irreps="32x0e+32x1o+32x2e+32x3o", readout_irreps="16x0e+16x1o+16x2e+16x3o"),
                                             "matrix_trunc_exp_2"),
                                            (dict(interaction_reduction="mean"), "matrix_power_2"),
-                                           ({}, "matrix_exp")])
+                                           ({}, "matrix_exp"),
+                                           (dict(lmax=3, hidden_irreps="128x0e+128x1o+128x2e+128x3o", readout_irreps="64x0e+64x1o+64x2e+64x3o"),
+                                            "matrix_power_2")])
 def test_parameter_gradients_match_oracle_autograd(cuda_device, over, positive):
-    ref, got, ref_loss, loss = _grads(over, 6, cuda_device, positive)
+    _check_grads(over, 4 if "128x0e" in over.get("hidden_irreps", "") else 6, cuda_device, positive)
+
+
+def test_parameter_gradients_128_lattices(cuda_device):
+    """a config-3 sized slice (BASELINE.json configs[2] trains on 512 lattices per GPU; 128 keeps the fp64 CPU autograd of the
+    oracle to seconds): long reductions over nodes / edges in the weight gradients."""
+    _check_grads({}, 128, cuda_device, "matrix_power_2")
+
+
+def _check_grads(over, n_lat, cuda_device, positive):
+    ref, got, ref_loss, loss = _grads(over, n_lat, cuda_device, positive)
     assert abs(loss - ref_loss) < 1e-5 * abs(ref_loss)
     assert set(got) == set(ref)
     worst = {}
@@ -44,4 +57,5 @@ def test_parameter_gradients_match_oracle_autograd(cuda_device, over, positive):
         assert g.shape == r.shape, k
         worst[k] = float((g - r).abs().max() / max(float(r.abs().max()), 1e-30))
     bad = {k: v for k, v in worst.items() if not v < GTOL}
+    print(f"gradient parity [{positive}, {n_lat} lattices, {over}]: worst {max(worst.values()):.2e} ({max(worst, key=worst.get)})")
     assert not bad, bad
