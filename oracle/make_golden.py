@@ -171,6 +171,34 @@ def mandel(ref):
                 mask=mod.mask.double(), rows=mod.rows, cols=mod.cols)
 
 
+def forward_fixtures(ref, cat, verbose=True):
+    """(ref_forward_lmax4, ref_variants, ref_forward_lmax3) fixtures, in memory (tests/test_golden_reproducible.py re-runs
+    this against the committed files)."""
+    say = print if verbose else (lambda *a, **k: None)
+    # mixed batch: 2 synthetic (N=6, one cubic cell, one orthorhombic) + real lattices with N in {1, 4, 6, 12}
+    real, seen = [], set()
+    for d in cat:
+        n = int(d["positions"].shape[0])
+        if n <= 12 and n not in seen:
+            seen.add(n)
+            real.append(to_lattice(d))
+    data = [synthetic_lattice(4000, 6), synthetic_lattice(4001, 7)] + real
+    batch = collate(data)
+    rmax = float(batch.edge_attr.max())
+    say(f"batch: {len(data)} lattices, N={batch.positions.shape[0]}, E={batch.edge_index.shape[1]}, names={[d.name for d in data]}")
+
+    say("reference forward lmax=4 (default hyper-parameters) ...")
+    variants = [dict(positive_function=f) for f in ("matrix_power_4", "matrix_trunc_exp_2", "matrix_trunc_exp_4", "none", "matrix_exp")]
+    variants.append(dict(global_reduction="sum"))
+    fix4, var4, _ = run_reference(ref, params_for(4, rmax), batch, seed=0, extra_params=variants)
+    fix4["lattice_names"] = [d.name for d in data]
+
+    say("reference forward lmax=3 ...")
+    fix3, _, _ = run_reference(ref, params_for(3, rmax), batch, seed=3)
+    fix3["lattice_names"] = [d.name for d in data]
+    return fix4, var4, fix3
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = refshim.install()
@@ -182,29 +210,9 @@ def main():
     print("Mandel fixtures ...")
     torch.save(mandel(ref), os.path.join(GOLD, "ref_mandel.pt"))
 
-    # mixed batch: 2 synthetic (N=6, one cubic cell, one orthorhombic) + real lattices with N in {1, 4, 6, 12}
-    real, seen = [], set()
-    for d in cat:
-        n = int(d["positions"].shape[0])
-        if n <= 12 and n not in seen:
-            seen.add(n)
-            real.append(to_lattice(d))
-    data = [synthetic_lattice(4000, 6), synthetic_lattice(4001, 7)] + real
-    batch = collate(data)
-    rmax = float(batch.edge_attr.max())
-    print(f"batch: {len(data)} lattices, N={batch.positions.shape[0]}, E={batch.edge_index.shape[1]}, names={[d.name for d in data]}")
-
-    print("reference forward lmax=4 (default hyper-parameters) ...")
-    variants = [dict(positive_function=f) for f in ("matrix_power_4", "matrix_trunc_exp_2", "matrix_trunc_exp_4", "none", "matrix_exp")]
-    variants.append(dict(global_reduction="sum"))
-    fix4, var4, _ = run_reference(ref, params_for(4, rmax), batch, seed=0, extra_params=variants)
-    fix4["lattice_names"] = [d.name for d in data]
+    fix4, var4, fix3 = forward_fixtures(ref, cat)
     torch.save(fix4, os.path.join(GOLD, "ref_forward_lmax4.pt"))
     torch.save(var4, os.path.join(GOLD, "ref_variants.pt"))
-
-    print("reference forward lmax=3 ...")
-    fix3, _, _ = run_reference(ref, params_for(3, rmax), batch, seed=3)
-    fix3["lattice_names"] = [d.name for d in data]
     torch.save(fix3, os.path.join(GOLD, "ref_forward_lmax3.pt"))
 
     print("reference tables ...")

@@ -1,7 +1,7 @@
 """GPU parity of the explicit backward: parameter gradients of the training loss (scripts/train_utils.py:45-64) from
 the CUDA module's `_bwd` kernels vs torch autograd through the fp64 CPU oracle, same weights, same synthetic lattices.
-Tolerance: 5e-5 of the largest entry of each gradient tensor (fp32 arithmetic with fixed-order reductions against fp64
-autograd; the measured worst case is recorded in profiles/)."""
+Tolerance: 3e-5 of the largest entry of each gradient tensor (fp32 arithmetic with fixed-order reductions against fp64
+autograd; measured worst case 2.3e-5 on 128 lattices, profiles/r02_gpu_tests_e.log)."""
 import pytest
 import torch
 
@@ -10,7 +10,7 @@ from energy_equiv_lattice_gnn_b200.train import relative_mse_loss, random_psd_ta
 from tests.util import batch_to, cuda_model_from, make_pair
 
 pytestmark = pytest.mark.gpu
-GTOL = 5e-5
+GTOL = 3e-5
 
 
 def _grads(lmax_over, n_lat, cuda_device, positive="matrix_power_2"):
