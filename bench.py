@@ -101,8 +101,24 @@ class ClockSampler:
         return out
 
 
+def fp32_peak():
+    """Measured fp32 FMA ceiling (TFLOP/s) of the B200: profiles/ffma2_rate.json, written by tools/micro/measure_fp32_peak.py."""
+    p = os.path.join(ROOT, "profiles", "ffma2_rate.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["fp32_tflops_peak"]), f"profiles/ffma2_rate.json ({d.get('source', '')}, {d.get('when', '')})"
+    except (OSError, ValueError, KeyError):
+        return 68.3, "fallback: round-1 measurement of tools/micro/ffma2_rate.cu (profiles/ffma2_rate.json missing)"
+
+
 def algorithmic_model(model, n_nodes: int, n_edges: int):
-    """Per-kernel algorithmic bytes / flops for one launch, keyed by timing tag."""
+    """Per-kernel ALGORITHMIC bytes / flops for one launch, keyed by timing tag.
+
+    L1.tp_scatter follows section 8(d)'s message+scatter figure: read h' [N,D,C] + edge inputs (Y, sender, CSR) + write the
+    message with interaction.linear folded ([N,D,C]) = 211 KB / 30-node lattice, + the streamed per-edge weights [E,P,C] =
+    856 KB / lattice (`bytes`: the built variant streams the weights).  `bytes_fused` is the 211 KB figure, `bytes_as_built`
+    adds what this implementation really moves (the un-folded M rows [N, 230, C])."""
     C, D = model.C, (model.lmax + 1) ** 2
     P1 = len(model._tp[-1]["paths"])
     rows1 = model._tp[-1]["rows_total"]
@@ -110,12 +126,15 @@ def algorithmic_model(model, n_nodes: int, n_edges: int):
     ncoef = model._wmap["n_coef"]
     N, E = n_nodes, n_edges
     f4 = 4
+    fused = f4 * (N * D * C + E * (D + 12) + (N + 1) + N * D * C)
     out = {
-        "L1.tp_scatter": dict(bytes=f4 * (N * D * C + E * (P1 * C + D + 1) + N * rows1 * C + N), flops=E * C * (2 * cg1 + 2 * rows1)),
-        "L1.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef),
-        "L0.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef),
-        "L1.radial_mlp": dict(bytes=f4 * (E * 12 + E * P1 * C + 2 * 64 * (64 + P1 * C)), flops=2 * E * (12 * 64 + 64 * 64 + 64 * P1 * C)),
-        "L1.interaction_linear": dict(bytes=f4 * (N * rows1 * C + N * D * C + rows1 * C * C // D), flops=2 * N * rows1 * C * C),
+        "L1.tp_scatter": dict(bytes=fused + f4 * E * P1 * C, bytes_fused=fused,
+                              bytes_as_built=f4 * (N * D * C + E * (P1 * C + D + 12) + N * rows1 * C + N + 1),
+                              flops=E * C * (2 * cg1 + 2 * rows1), bound="hbm"),
+        "L1.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef, bound="fp32"),
+        "L0.sym_contract": dict(bytes=f4 * (2 * N * D * C + ncoef * C), flops=N * C * 2 * ncoef, bound="fp32"),
+        "L1.radial_mlp": dict(bytes=f4 * (E * 12 + E * P1 * C + 2 * 64 * (64 + P1 * C)), flops=2 * E * (12 * 64 + 64 * 64 + 64 * P1 * C), bound="hbm"),
+        "L1.interaction_linear": dict(bytes=f4 * (N * rows1 * C + N * D * C + rows1 * C * C // D), flops=2 * N * rows1 * C * C, bound="hbm"),
     }
     return out
 
@@ -170,6 +189,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg (BASELINE.json configs[2])")
     ap.add_argument("--train-lattices", type=int, default=512, help="lattices per GPU per training step")
+    ap.add_argument("--sharded", action="store_true",
+                    help="build ONE global batch of gpus x lattices lattices and give every rank its edge-balanced shard through "
+                         "sharding.shard_batch (default for --config 5); otherwise every rank generates its own batch (weak scaling)")
+    ap.add_argument("--no-small-batch", action="store_true", help="skip the batch-64 CUDA-graph leg")
+    ap.add_argument("--small-batch", type=int, default=64, help="lattices per step of the small-batch leg (scripts/train_main.py:42)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -190,6 +214,11 @@ def main():
     if args.config != 2:
         args.no_train = True
         args.no_cpu_baseline = True
+        args.no_small_batch = True
+    if args.config == 5:
+        args.sharded = True
+    config["sharding"] = ("one global batch of gpus x lattices_per_gpu lattices, contiguous edge-balanced shards (sharding.shard_batch), no "
+                          "data-path collective") if args.sharded else "every rank generates its own lattices_per_gpu batch (independent units)"
 
     if args.impl == "reference":
         if rank != 0:
@@ -225,9 +254,21 @@ def main():
     G = args.lattices
     host_batches = []
     rmax = 0.0
+    shard_info = None
     for k in range(2):
-        if args.config == 5:   # 216-node lattices are slow to generate on the host: 32 distinct ones, tiled
-            from energy_equiv_lattice_gnn_b200.data import collate, synthetic_lattice
+        from energy_equiv_lattice_gnn_b200.data import collate, synthetic_lattice
+        if args.sharded:
+            # the SAME global batch on every rank (seeded), then this rank's shard
+            from energy_equiv_lattice_gnn_b200.sharding import shard_batch
+            Gg = G * world
+            n_distinct = min(32 if n_nodes_lat > 64 else 256, Gg)
+            distinct = [synthetic_lattice(cfg[2] + k * n_distinct + i, n_nodes_lat) for i in range(n_distinct)]
+            gb = collate([distinct[i % n_distinct] for i in range(Gg)])
+            r = max(float(d.edge_attr.max()) for d in distinct)
+            b, (g0, g1) = shard_batch(gb, rank, world)
+            shard_info = {"global_lattices": Gg, "range": [g0, g1], "nodes": int(b.positions.shape[0]), "edges": int(b.edge_index.shape[1])}
+            del gb
+        elif args.config == 5:   # 216-node lattices are slow to generate on the host: 32 distinct ones, tiled
             distinct = [synthetic_lattice(cfg[2] + (2 * rank + k) * 32 + i, n_nodes_lat) for i in range(min(32, G))]
             data = [distinct[i % len(distinct)] for i in range(G)]
             b, r = collate(data), max(float(d.edge_attr.max()) for d in distinct)
@@ -236,6 +277,7 @@ def main():
             b, r = synthetic_batch(range(seed0, seed0 + G), n_nodes_lat)
         host_batches.append(b.pin_memory())
         rmax = max(rmax, r)
+    G = int(host_batches[0].num_graphs)   # sharded: this rank's share
     params = default_params(max_edge_radius=rmax, **cfg[3])
     torch.manual_seed(0)
     model = EnergyEquivGNN(params).to(dev).eval()
@@ -315,21 +357,60 @@ def main():
     step_sum = sum(kern.values())
     alg = algorithmic_model(model, n_nodes, n_edges)
     peak, peak_src = measured_peaks()
-    # dominant kernel among the memory-streaming ones (north_star: message / scatter kernels vs the HBM roofline); the
-    # symmetric contraction is fp32-FMA bound with ~0.2 GB of traffic, a bytes roofline says nothing about it - it is listed
-    # with its TFLOP/s under "kernels" (68.3 TFLOP/s measured FFMA2 peak)
-    top = max((k for k in kern if k in alg and "sym_contract" not in k), key=lambda k: kern[k])
+    # north_star: the message / scatter kernel against the HBM roofline (bytes of SURVEY.md section 8(d)); the symmetric
+    # contraction is fp32-FMA bound and gets its own entry against the measured fp32 ceiling (roofline_kernels)
+    top = "L1.tp_scatter" if "L1.tp_scatter" in kern else max((k for k in kern if k in alg), key=lambda k: kern[k])
     top_ms = kern[top]
     achieved = alg[top]["bytes"] / (top_ms * 1e-3) / 1e9
     traffic, traffic_src = ncu_traffic(top, n_nodes, n_edges)
+    fpeak, fpeak_src = fp32_peak()
     roofline = {"kernel": top, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "ms_per_launch": top_ms, "share_of_step": top_ms / step_sum,
-                "algorithmic_bytes_per_launch": alg[top]["bytes"], "algorithmic_flops_per_launch": alg[top]["flops"],
-                "fp32_tflops_achieved": alg[top]["flops"] / (top_ms * 1e-3) / 1e12,
-                "fp32_tflops_peak_measured": 68.3, "fp32_peak_source": "tools/micro/ffma2_rate.cu on B200: 2.17 clk per FFMA2 per SMSP at 1.95 GHz",
-                "note": "kernel is fp32-FMA bound, not HBM bound (SURVEY.md App. C); bytes-based fraction reported as the contract asks"}
+                "algorithmic_bytes_per_launch": alg[top]["bytes"],
+                "algorithmic_bytes_note": "SURVEY 8(d) message+scatter, streamed per-edge weights: 856 KB per 30-node lattice",
+                "frac_fused_211KB": alg[top].get("bytes_fused", 0) / (top_ms * 1e-3) / 1e9 / peak,
+                "as_built_bytes_per_launch": alg[top].get("bytes_as_built"),
+                "algorithmic_flops_per_launch": alg[top]["flops"],
+                "fp32_tflops_achieved": alg[top]["flops"] / (top_ms * 1e-3) / 1e12, "fp32_tflops_peak_measured": fpeak,
+                "fp32_frac": alg[top]["flops"] / (top_ms * 1e-3) / 1e12 / fpeak, "fp32_peak_source": fpeak_src,
+                "limiter": "issue / shared-memory broadcast bound (lane = channel: one LDS.128 of the per-edge G matrix per 4 FMAs), "
+                           "not HBM: profiles/r01_ncu_tp_fwd_s13_summary.txt"}
+    roofline_kernels = []
+    for k in sorted((k for k in kern if k in alg), key=lambda k: -kern[k]):
+        t = kern[k] * 1e-3
+        ent = {"kernel": k, "ms_per_launch": kern[k], "share_of_step": kern[k] / step_sum, "bound": alg[k]["bound"],
+               "GBps": alg[k]["bytes"] / t / 1e9, "hbm_frac": alg[k]["bytes"] / t / 1e9 / peak,
+               "fp32_tflops": alg[k]["flops"] / t / 1e12, "fp32_frac": alg[k]["flops"] / t / 1e12 / fpeak}
+        roofline_kernels.append(ent)
     kernels = {k: {"ms": round(v, 4), **({"GBps": round(alg[k]["bytes"] / v / 1e6, 1), "TFLOPs": round(alg[k]["flops"] / v / 1e9, 2)} if k in alg else {})}
                for k, v in sorted(kern.items(), key=lambda kv: -kv[1])}
+
+    # ---- small-batch leg: the reference's batch size (scripts/train_main.py:42), eager vs CUDA-graph replay, pinned host in / out
+    small = None
+    if not args.no_small_batch:
+        from energy_equiv_lattice_gnn_b200.serve import GraphedPredictor
+        Gs = args.small_batch
+        sb = [synthetic_batch(range(40000 + (2 * rank + k) * Gs, 40000 + (2 * rank + k) * Gs + Gs), N_NODES)[0].pin_memory() for k in range(2)]
+        host_out = torch.empty(Gs, 6, 6, pin_memory=True)
+        gp = GraphedPredictor(model)
+
+        def eager(i):
+            host_out.copy_(model(sb[i % 2].to(dev, non_blocking=True))["stiffness"], non_blocking=True)
+
+        def graphed(i):
+            gp(sb[i % 2], sync=False)
+
+        k_small = max(args.steps, 50)
+        l2 = native.launch_count
+        ms_eager = timed(eager, k_small, 5) / k_small
+        launches_small = (native.launch_count - l2) // (k_small + 5)
+        ms_graph = timed(graphed, k_small, 5) / k_small
+        small = {"lattices_per_step": Gs, "eager": {"value": world * Gs / (ms_eager * 1e-3), "unit": UNIT, "ms_per_step": ms_eager,
+                                                    "kernel_launches_per_step": launches_small},
+                 "cuda_graph": {"value": world * Gs / (ms_graph * 1e-3), "unit": UNIT, "ms_per_step": ms_graph,
+                                "graph_launches_per_step": 1, "kernels_in_graph": launches_small},
+                 "speedup": ms_eager / ms_graph,
+                 "note": "pinned host batch -> H2D -> forward -> D2H of [G,6,6] every step; same kernels, replayed as one CUDA graph"}
 
     # ---- training step (BASELINE.json configs[2]): fwd + loss + explicit backward + flat all-reduce + clip + AdamW(amsgrad)
     train = None
@@ -372,13 +453,18 @@ def main():
             dist.destroy_process_group()
         return
     ms_step = ms_total / args.steps
-    value = world * G / (ms_step * 1e-3)
+    total_lattices = shard_info["global_lattices"] if shard_info else world * G
+    value = total_lattices / (ms_step * 1e-3)
+    if shard_info:
+        config["shard_rank0"] = shard_info
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": config, "clocks": clocks,
-            "e2e": {"value": world * G / (ms_e2e / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "e2e": {"value": total_lattices / (ms_e2e / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": launches_timed, "roofline": roofline, "kernels": kernels}
+            "gpu_launches": launches_timed, "roofline": roofline, "roofline_kernels": roofline_kernels, "kernels": kernels}
+    if small is not None:
+        line["small_batch"] = small
     if train is not None:
         line["train_step"] = train
     if world == 1 and not args.no_cpu_baseline:
