@@ -24,7 +24,7 @@ SYMBOLS = [
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
     "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
     "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd", "eeg_segment_sum_rows",
-    "eeg_block_linear_wgrad_ws_floats",
+    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd",
 ]
 
 
@@ -512,6 +512,16 @@ def collate_gather(ds_pos, ds_nattr, ds_snd, ds_rcv, ds_shifts, ds_eattr, meta, 
                                     _p(graph_idx, i64) if graph_idx is not None else C.c_void_p(0), C.c_int64(width), _p(o_g), _stream()),
            "eeg_collate_gather")
     return o_pos, o_na, o_ei, o_sh, o_ea, o_b, o_g
+
+
+def radial_embedding(edge_lengths, num_bessel: int, r_max: float, num_polynomial_cutoff: int) -> torch.Tensor:
+    """RadialEmbeddingBlock.forward (gnn/blocks.py:96-102): [E,1] or [E] -> [E, num_bessel]."""
+    x = edge_lengths.reshape(-1).contiguous()
+    out = torch.empty(x.shape[0], num_bessel, dtype=f32, device=x.device)
+    _begin("eeg_radial_embedding_fwd")
+    _check(lib().eeg_radial_embedding_fwd(_p(x, f32), C.c_int64(x.shape[0]), C.c_int(num_bessel), C.c_float(r_max),
+                                          C.c_int(num_polynomial_cutoff), _p(out), _stream()), "eeg_radial_embedding_fwd")
+    return out
 
 
 def rand_rotations(seed: int, offset: int, G: int, device) -> torch.Tensor:

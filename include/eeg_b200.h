@@ -231,6 +231,11 @@ int eeg_collate_gather(const float* pos, const float* node_attrs, const int32_t*
  * Q = Ry(alpha) Rx(beta) Ry(gamma); counter-based generator: lattice g of the call uses counters 3*(offset+g) .. +2. */
 int eeg_rand_rotations(uint64_t seed, uint64_t offset, int64_t G, float* Q /*[G,3,3]*/, void* stream);
 
+/* ---- RadialEmbeddingBlock (gnn/blocks.py:89-102): BesselBasis (gnn/mace.py:28-71) x PolynomialCutoff (gnn/mace.py:74-106).
+ * edge_lengths [E] -> out [E, num_bessel].  Defined by the reference, not used by EnergyEquivGNN. */
+int eeg_radial_embedding_fwd(const float* edge_lengths, int64_t E, int num_bessel, float r_max, int num_polynomial_cutoff,
+                             float* out, void* stream);
+
 /* ---- validation / test metrics (scripts/train_utils.py:66-89 validation_step, :149-172 obtain_errors; SURVEY.md 8(f)
  * rank 3).  pred, target: Mandel [G,6,6]; directions: [P,3] unit vectors.  per_lattice [G,4] = (mean squared error and mean
  * absolute error over the 36 entries (:157-158), mean_p |c(d_p) - c_pred(d_p)| (:161-163), mean_p c(d_p) of the target
