@@ -385,6 +385,43 @@ def main():
     kernels = {k: {"ms": round(v, 4), **({"GBps": round(alg[k]["bytes"] / v / 1e6, 1), "TFLOPs": round(alg[k]["flops"] / v / 1e9, 2)} if k in alg else {})}
                for k, v in sorted(kern.items(), key=lambda kv: -kv[1])}
 
+    # ---- training step (BASELINE.json configs[2]): fwd + loss + explicit backward + flat all-reduce + clip + AdamW(amsgrad)
+    train = None
+    if not args.no_train:
+        from energy_equiv_lattice_gnn_b200.train import Trainer, random_psd_targets
+        Gt = args.train_lattices
+        tb_, _ = synthetic_batch(range(10000 + Gt * rank, 10000 + Gt * rank + Gt), N_NODES)
+        tb_ = tb_.to(dev)
+        tb_.stiffness = random_psd_targets(Gt, seed=rank).to(dev)
+        torch.manual_seed(0)
+        tmodel = EnergyEquivGNN(params).to(dev)
+        trainer = Trainer(tmodel)
+        k_train = min(args.steps, 10)
+        l1 = native.launch_count
+        for _ in range(5):
+            trainer.training_step(tb_)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k_train):
+            loss = trainer.training_step(tb_)
+        e1.record()
+        barrier()
+        ms_t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if dist is not None:
+            dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+        native.start_profile()
+        trainer.training_step(tb_)
+        tprof = {k: sum(v) for k, v in native.stop_profile().items()}
+        ms_train = float(ms_t.item()) / k_train
+        train = {"metric": "lattices/sec training step (fwd + loss + backward + gradient all-reduce + clip + AdamW amsgrad)",
+                 "value": world * Gt / (ms_train * 1e-3), "unit": UNIT, "ms_per_step": ms_train, "lattices_per_gpu": Gt, "steps": k_train,
+                 "warmup": 5, "loss_last": float(loss), "gpu_launches_per_step": (native.launch_count - l1) // (k_train + 6),
+                 "allreduce_bytes_per_step": trainer.opt.grad.numel() * 4 if world > 1 else 0,
+                 "kernels_ms": {k: round(v, 4) for k, v in sorted(tprof.items(), key=lambda kv: -kv[1])[:24]},
+                 "deterministic": "fixed-order reductions everywhere (no atomics): two runs give bitwise identical gradients",
+                 "workload": "BASELINE.json configs[2]: default hyper-parameters, random PSD targets, relative-MSE loss, no accumulation"}
+        del trainer, tmodel
     # ---- small-batch leg: the reference's batch size (scripts/train_main.py:42), eager vs CUDA-graph replay, pinned host in / out
     small = None
     if not args.no_small_batch:
@@ -412,42 +449,6 @@ def main():
                  "speedup": ms_eager / ms_graph,
                  "note": "pinned host batch -> H2D -> forward -> D2H of [G,6,6] every step; same kernels, replayed as one CUDA graph"}
 
-    # ---- training step (BASELINE.json configs[2]): fwd + loss + explicit backward + flat all-reduce + clip + AdamW(amsgrad)
-    train = None
-    if not args.no_train:
-        from energy_equiv_lattice_gnn_b200.train import Trainer, random_psd_targets
-        Gt = args.train_lattices
-        tb_, _ = synthetic_batch(range(10000 + Gt * rank, 10000 + Gt * rank + Gt), N_NODES)
-        tb_ = tb_.to(dev)
-        tb_.stiffness = random_psd_targets(Gt, seed=rank).to(dev)
-        torch.manual_seed(0)
-        tmodel = EnergyEquivGNN(params).to(dev)
-        trainer = Trainer(tmodel)
-        k_train = min(args.steps, 10)
-        l1 = native.launch_count
-        for _ in range(3):
-            trainer.training_step(tb_)
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(k_train):
-            loss = trainer.training_step(tb_)
-        e1.record()
-        barrier()
-        ms_t = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if dist is not None:
-            dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
-        native.start_profile()
-        trainer.training_step(tb_)
-        tprof = {k: sum(v) for k, v in native.stop_profile().items()}
-        ms_train = float(ms_t.item()) / k_train
-        train = {"metric": "lattices/sec training step (fwd + loss + backward + gradient all-reduce + clip + AdamW amsgrad)",
-                 "value": world * Gt / (ms_train * 1e-3), "unit": UNIT, "ms_per_step": ms_train, "lattices_per_gpu": Gt, "steps": k_train,
-                 "warmup": 3, "loss_last": float(loss), "gpu_launches_per_step": (native.launch_count - l1) // (k_train + 4),
-                 "allreduce_bytes_per_step": trainer.opt.grad.numel() * 4 if world > 1 else 0,
-                 "kernels_ms": {k: round(v, 4) for k, v in sorted(tprof.items(), key=lambda kv: -kv[1])[:16]},
-                 "workload": "BASELINE.json configs[2]: default hyper-parameters, random PSD targets, relative-MSE loss, no accumulation"}
-        del trainer, tmodel
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
