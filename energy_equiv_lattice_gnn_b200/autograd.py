@@ -59,7 +59,10 @@ def _mlp_backward(lins: List[torch.nn.Linear], f, dw, E, lay_f, lay_h, lay_w, gr
         lay_in = lay_h
     last = lins[-1]
     W2 = last.weight.detach()  # [n_out, H]
-    grads[id(last.weight)] = nv.linear_wgrad(dw, lay_w, act[-1], lay_h, [0], [1.0], W2.numel(), E)[0].view_as(W2)
+    lay_last = lay_f if len(lins) == 1 else lay_h   # single-layer MLP: the edge features feed the last linear directly
+    grads[id(last.weight)] = nv.linear_wgrad(dw, lay_w, act[-1], lay_last, [0], [1.0], W2.numel(), E)[0].view_as(W2)
+    if len(lins) == 1:
+        return
     ds = nv.block_linear(dw, lay_w, W2.reshape(-1), [0], [1.0], lay_h, E)
     for k in range(len(lins) - 2, -1, -1):
         lin = lins[k]

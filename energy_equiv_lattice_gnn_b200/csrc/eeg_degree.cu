@@ -35,3 +35,31 @@ extern "C" int eeg_scale_rows_inv_degree(float* x, const int32_t* row_ptr, int64
   EEG_CHECK_LAUNCH("eeg_scale_rows_inv_degree");
   return 0;
 }
+
+// [E, B, 32] (edge-major per-edge tensor-product weights, as a generic radial MLP writes them) -> [B, E, 32] (path-major w_t,
+// the layout eeg_tp_scatter_fwd / _bwd read).  Only used when the radial MLP is outside the fused tcgen05 kernel's shape
+// (inter_MLP_dim != 64, more than 16 edge bases, a single layer).
+namespace {
+__global__ void k_blocks32_transpose(const float4* __restrict__ in, float4* __restrict__ out, int64_t E, int B, int to_path_major) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // float4 index of the destination
+  if (i >= E * B * 8) return;
+  const int q = (int)(i & 7);
+  const int64_t r = i >> 3;
+  if (to_path_major) {   // dst [B, E]: r = b * E + e
+    const int64_t b = r / E, e = r - b * E;
+    out[i] = __ldg(in + (e * B + b) * 8 + q);
+  } else {               // dst [E, B]: r = e * B + b
+    const int64_t e = r / B, b = r - e * B;
+    out[i] = __ldg(in + (b * E + e) * 8 + q);
+  }
+}
+}  // namespace
+
+extern "C" int eeg_blocks32_transpose(const float* in, float* out, int64_t E, int B, int to_path_major, void* stream) {
+  if (E == 0 || B == 0) return 0;
+  const int64_t tot = E * B * 8;
+  k_blocks32_transpose<<<(unsigned)eeg_div_up(tot, 256), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(in),
+                                                                                          reinterpret_cast<float4*>(out), E, B, to_path_major);
+  EEG_CHECK_LAUNCH("eeg_blocks32_transpose");
+  return 0;
+}

@@ -3,8 +3,7 @@
 // (gnn/mace.py:338-352), soft_one_hot_linspace x2 and o3.SphericalHarmonics (gnn/model.py:146-157).
 #include <stdarg.h>
 #include "eeg_common.cuh"
-#include "generated/sh_l3.cuh"
-#include "generated/sh_l4.cuh"
+#include "generated/all_sh.cuh"
 
 static thread_local char g_err[512] = "";
 void eeg_set_error(const char* fmt, ...) {
@@ -171,17 +170,18 @@ extern "C" int eeg_graph_ptr(const int64_t* batch, int64_t N, int64_t G, int32_t
 // ---------------------------------------------------------------------------------------------------------------
 template <int LMAX>
 __device__ __forceinline__ void sh_eval(float x, float y, float z, float* Y);
-template <>
-__device__ __forceinline__ void sh_eval<3>(float x, float y, float z, float* Y) { eeg_sh_l3(x, y, z, Y); }
-template <>
-__device__ __forceinline__ void sh_eval<4>(float x, float y, float z, float* Y) { eeg_sh_l4(x, y, z, Y); }
+#define EEG_X(L) \
+  template <>    \
+  __device__ __forceinline__ void sh_eval<L>(float x, float y, float z, float* Y) { eeg_sh_l##L(x, y, z, Y); }
+EEG_LMAX_LIST(EEG_X)
+#undef EEG_X
 
 template <int LMAX, int NB>
 __global__ void __launch_bounds__(128) k_edge_featurize(const float* __restrict__ pos, const int64_t* __restrict__ edge_index,
                                                         const float* __restrict__ shifts, const float* __restrict__ radius,
                                                         const int32_t* __restrict__ perm, int64_t E, float len_end, float rmax,
                                                         float* __restrict__ Yout, int ystride, float* __restrict__ fout,
-                                                        int32_t* __restrict__ sender_sorted) {
+                                                        int32_t* __restrict__ sender_sorted, int nb_rt) {
   constexpr int D = (LMAX + 1) * (LMAX + 1);
   constexpr int DP = (D + 3) / 4 * 4;
   int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -202,7 +202,19 @@ __global__ void __launch_bounds__(128) k_edge_featurize(const float* __restrict_
 #pragma unroll
   for (int k = 0; k < DP / 4; ++k) yo[k] = make_float4(Y[4 * k], Y[4 * k + 1], Y[4 * k + 2], Y[4 * k + 3]);
   // soft_one_hot_linspace(gaussian): exp(-((x - k*step)/step)^2) / 1.12, step = end/(NB-1)
-  float f[2 * NB];
+  if constexpr (NB == 0) {   // any number of bases (num_edge_bases is a free hyper-parameter, gnn/model.py:146-152)
+    const float r = __ldg(radius + e);
+    const float sl = len_end / (float)(nb_rt - 1), sr = rmax / (float)(nb_rt - 1);
+    float* fo = fout + j * (int64_t)(2 * nb_rt);
+    for (int k = 0; k < nb_rt; ++k) {
+      const float dl = (len - (float)k * sl) / sl, dr = (r - (float)k * sr) / sr;
+      fo[k] = expf(-dl * dl) / 1.12f;
+      fo[nb_rt + k] = expf(-dr * dr) / 1.12f;
+    }
+    sender_sorted[j] = (int32_t)snd;
+    return;
+  }
+  float f[2 * (NB ? NB : 1)];
   const float r = __ldg(radius + e);
   const float sl = len_end / (float)(NB - 1), sr = rmax / (float)(NB - 1);
 #pragma unroll
@@ -235,12 +247,23 @@ extern "C" int eeg_edge_featurize(const float* pos, const int64_t* edge_index, c
 #define EEG_EF(L, NBV)                                                                                              \
   if (lmax == L && nbasis == NBV) {                                                                                 \
     k_edge_featurize<L, NBV><<<g, b, 0, s>>>(pos, edge_index, shifts, radius, perm, E, len_end, rmax, Y, ystride, f, \
-                                              sender_sorted);                                                       \
+                                              sender_sorted, nbasis);                                               \
     EEG_CHECK_LAUNCH("eeg_edge_featurize");                                                                         \
     return 0;                                                                                                       \
   }
-  EEG_EF(4, 6) EEG_EF(3, 6) EEG_EF(4, 8) EEG_EF(3, 8) EEG_EF(4, 4) EEG_EF(3, 4)
+  EEG_REQUIRE(nbasis >= 2, "eeg_edge_featurize: num_edge_bases must be >= 2 (got %d)", nbasis);
+#define EEG_X(L) EEG_EF(L, 6) EEG_EF(L, 8) EEG_EF(L, 4)
+  EEG_LMAX_LIST(EEG_X)
+#undef EEG_X
 #undef EEG_EF
+#define EEG_X(L)                                                                                                       \
+  if (lmax == L) {                                                                                                     \
+    k_edge_featurize<L, 0><<<g, b, 0, s>>>(pos, edge_index, shifts, radius, perm, E, len_end, rmax, Y, ystride, f, sender_sorted, nbasis); \
+    EEG_CHECK_LAUNCH("eeg_edge_featurize");                                                                            \
+    return 0;                                                                                                          \
+  }
+  EEG_LMAX_LIST(EEG_X)
+#undef EEG_X
   eeg_set_error("eeg_edge_featurize: unsupported (lmax=%d, nbasis=%d)", lmax, nbasis);
   return 1;
 }

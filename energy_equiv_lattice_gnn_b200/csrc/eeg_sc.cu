@@ -36,9 +36,9 @@ __global__ void __launch_bounds__(256) k_sc_coefficients(const int32_t* __restri
 
 }  // namespace
 
-int eeg_sc_launch_s1(int lmax, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s);
-int eeg_sc_launch_p2(int lmax, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s);
-int eeg_sc_launch_p2a(int lmax, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s);
+int eeg_sc_launch_s1(int lmax, int nu, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s);
+int eeg_sc_launch_p2(int lmax, int nu, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s);
+int eeg_sc_launch_p2a(int lmax, int nu, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s);
 
 extern "C" int eeg_sc_coefficients(const int32_t* a_row_ptr, const int32_t* a_col, const float* a_val, int n_coef,
                                    const float* Wflat, int C, float* T, void* stream) {
@@ -50,15 +50,15 @@ extern "C" int eeg_sc_coefficients(const int32_t* a_row_ptr, const int32_t* a_co
 }
 
 extern "C" int eeg_sym_contract_fwd(int lmax, int nu, int C, const float* x, const float* T, float* out, int64_t N, void* stream) {
-  EEG_REQUIRE(nu == 3, "eeg_sym_contract_fwd: unsupported correlation=%d (generated: 3)", nu);
-  EEG_REQUIRE(lmax == 3 || lmax == 4, "eeg_sym_contract_fwd: unsupported lmax=%d (generated: 3, 4)", lmax);
+  EEG_REQUIRE(nu >= 1 && nu <= 3, "eeg_sym_contract_fwd: unsupported correlation=%d (generated: 1..3)", nu);
+  EEG_REQUIRE(lmax >= 1 && lmax <= 4, "eeg_sym_contract_fwd: unsupported lmax=%d (generated: 1..4)", lmax);
   if (N == 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
   // Variants (eeg_sc_v_*.cu) run the same fp32 FMA sequence per node => bit-identical results.  Measured on B200
   // (N = 30720, C = 32): lmax 4: s1 647 us, p2 525 us, p2a 492 us; lmax 3: s1 203 us, p2 148 us, p2a 196 us.
   static const char* env = getenv("EEG_SC_VARIANT");  // tuning / A-B knob
-  const int v = !env ? (lmax == 4 ? 2 : 1) : !strcmp(env, "s1") ? 0 : !strcmp(env, "p2") ? 1 : 2;
-  if (v == 0) return eeg_sc_launch_s1(lmax, C, x, T, out, N, s);
-  if (v == 1) return eeg_sc_launch_p2(lmax, C, x, T, out, N, s);
-  return eeg_sc_launch_p2a(lmax, C, x, T, out, N, s);
+  const int v = !env ? (lmax == 4 && nu == 3 ? 2 : 1) : !strcmp(env, "s1") ? 0 : !strcmp(env, "p2") ? 1 : 2;
+  if (v == 0) return eeg_sc_launch_s1(lmax, nu, C, x, T, out, N, s);
+  if (v == 1) return eeg_sc_launch_p2(lmax, nu, C, x, T, out, N, s);
+  return eeg_sc_launch_p2a(lmax, nu, C, x, T, out, N, s);
 }

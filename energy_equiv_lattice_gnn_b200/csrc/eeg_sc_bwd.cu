@@ -4,8 +4,7 @@
 //                            coefficient stream as the forward (generated macro program, packed FFMA2 on node pairs)
 // (weight gradient: eeg_sc_wgrad.cu)
 #include "eeg_common.cuh"
-#include "generated/scb_l3_nu3.cuh"
-#include "generated/scb_l4_nu3.cuh"
+#include "generated/all_scb.cuh"
 
 namespace {
 
@@ -29,32 +28,26 @@ __device__ __forceinline__ void unpk(p2 v, float& a, float& b) { asm("mov.b64 {%
 #define E2(j) m1 = ffma2(m2, x[j], m1); dx[j] = ffma2(gi, m2, dx[j]);
 #define E1(i) dx[i] = ffma2(g, m1, dx[i]);
 
-template <int LMAX>
+template <int LMAX, int NU>
 struct ProgB;
-template <>
-struct ProgB<4> {
-  static constexpr int NCOEF = EEG_SCB_l4_nu3_NCOEF, D = 25;
-  static __device__ __forceinline__ void run(const p2* __restrict__ x, p2* __restrict__ dx, const float4* __restrict__ T4,
-                                             const float* __restrict__ dsin) {
-    p2 g, gi, gij, m1, m2;
-    EEG_SCB_l4_nu3_PROGRAM
-  }
-};
-template <>
-struct ProgB<3> {
-  static constexpr int NCOEF = EEG_SCB_l3_nu3_NCOEF, D = 16;
-  static __device__ __forceinline__ void run(const p2* __restrict__ x, p2* __restrict__ dx, const float4* __restrict__ T4,
-                                             const float* __restrict__ dsin) {
-    p2 g, gi, gij, m1, m2;
-    EEG_SCB_l3_nu3_PROGRAM
-  }
-};
+#define EEG_X(L, N)                                                                                                        \
+  template <>                                                                                                              \
+  struct ProgB<L, N> {                                                                                                     \
+    static constexpr int NCOEF = EEG_SCB_l##L##_nu##N##_NCOEF, D = (L + 1) * (L + 1);                                        \
+    static __device__ __forceinline__ void run(const p2* __restrict__ x, p2* __restrict__ dx, const float4* __restrict__ T4, \
+                                               const float* __restrict__ dsin) {                                           \
+      p2 g, gi, gij, m1, m2;                                                                                               \
+      EEG_SCB_l##L##_nu##N##_PROGRAM                                                                                       \
+    }                                                                                                                      \
+  };
+EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
 
-template <int LMAX>
+template <int LMAX, int NU>
 __global__ void __launch_bounds__(THREADS, 1) k_sc_bwd_x(const float* __restrict__ xg, const float* __restrict__ dog,
                                                          const float* __restrict__ T, float* __restrict__ dxg, int64_t N, int C,
                                                          int tiles_per_cta) {
-  using F = ProgB<LMAX>;
+  using F = ProgB<LMAX, NU>;
   constexpr int D = F::D, NCOEF = F::NCOEF;
   extern __shared__ __align__(16) float smem[];
   float* Ts = smem;                     // [CH][NCOEF]
@@ -111,13 +104,13 @@ __global__ void __launch_bounds__(THREADS, 1) k_sc_bwd_x(const float* __restrict
   }
 }
 
-template <int LMAX>
+template <int LMAX, int NU>
 int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float* dx, int64_t N, cudaStream_t s) {
-  using F = ProgB<LMAX>;
+  using F = ProgB<LMAX, NU>;
   const size_t smem = (size_t)(CH * F::NCOEF + 2 * CH * F::D * NT) * sizeof(float);
   static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_sc_bwd_x<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_sc_bwd_x<LMAX, NU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
       eeg_set_error("eeg_sym_contract_bwd_x: cannot opt in to %zu B shared memory: %s", smem, cudaGetErrorString(e));
       return 2;
@@ -131,7 +124,7 @@ int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float
   if (slices < 1) slices = 1;
   const int tiles_per_cta = (int)((n_tiles + slices - 1) / slices);
   slices = (int)((n_tiles + tiles_per_cta - 1) / tiles_per_cta);
-  k_sc_bwd_x<LMAX><<<dim3(groups, slices), THREADS, smem, s>>>(x, dout, T, dx, N, C, tiles_per_cta);
+  k_sc_bwd_x<LMAX, NU><<<dim3(groups, slices), THREADS, smem, s>>>(x, dout, T, dx, N, C, tiles_per_cta);
   EEG_CHECK_LAUNCH("eeg_sym_contract_bwd_x");
   return 0;
 }
@@ -140,8 +133,12 @@ int launch_bwd_x(int C, const float* x, const float* dout, const float* T, float
 
 extern "C" int eeg_sym_contract_bwd_x(int lmax, int nu, int C, const float* x, const float* dout, const float* T, float* dx,
                                       int64_t N, void* stream) {
-  EEG_REQUIRE(nu == 3 && (lmax == 3 || lmax == 4), "eeg_sym_contract_bwd_x: unsupported (lmax=%d, correlation=%d)", lmax, nu);
+  EEG_REQUIRE(nu >= 1 && nu <= 3 && lmax >= 1 && lmax <= 4, "eeg_sym_contract_bwd_x: unsupported (lmax=%d, correlation=%d)", lmax, nu);
   EEG_REQUIRE(C > 0 && C % CH == 0, "eeg_sym_contract_bwd_x: C must be a multiple of %d", CH);
   if (N == 0) return 0;
-  return lmax == 4 ? launch_bwd_x<4>(C, x, dout, T, dx, N, (cudaStream_t)stream) : launch_bwd_x<3>(C, x, dout, T, dx, N, (cudaStream_t)stream);
+#define EEG_X(L, NN) \
+  if (lmax == L && nu == NN) return launch_bwd_x<L, NN>(C, x, dout, T, dx, N, (cudaStream_t)stream);
+  EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
+  return 1;
 }

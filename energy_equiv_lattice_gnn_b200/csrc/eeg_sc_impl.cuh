@@ -16,8 +16,7 @@
 #ifndef EEG_SC_V_MINB
 #define EEG_SC_V_MINB 1  // resident CTAs per SM (2: one CTA does tile I/O while the other computes)
 #endif
-#include "generated/sc_l3_nu3.cuh"
-#include "generated/sc_l4_nu3.cuh"
+#include "generated/all_sc.cuh"
 
 namespace {
 
@@ -92,26 +91,21 @@ typedef p2 xreg;
 #error "unsupported symmetric-contraction variant"
 #endif
 
-template <int LMAX>
+template <int LMAX, int NU>
 struct Prog;
-template <>
-struct Prog<4> {
-  static constexpr int NCOEF = EEG_SC_l4_nu3_NCOEF, D = 25;
-  static __device__ __forceinline__ void run(const xreg* __restrict__ x, const float4* __restrict__ T4, float* __restrict__ out,
-                                             int ostride = 0, int64_t vstride = 0, bool ok0 = true, bool ok1 = true) {
-    SC_DECL
-    EEG_SC_l4_nu3_PROGRAM
-  }
-};
-template <>
-struct Prog<3> {
-  static constexpr int NCOEF = EEG_SC_l3_nu3_NCOEF, D = 16;
-  static __device__ __forceinline__ void run(const xreg* __restrict__ x, const float4* __restrict__ T4, float* __restrict__ out,
-                                             int ostride = 0, int64_t vstride = 0, bool ok0 = true, bool ok1 = true) {
-    SC_DECL
-    EEG_SC_l3_nu3_PROGRAM
-  }
-};
+// one specialisation per generated (lmax, correlation) program (generated/registry.cuh)
+#define EEG_X(L, N)                                                                                                          \
+  template <>                                                                                                                \
+  struct Prog<L, N> {                                                                                                        \
+    static constexpr int NCOEF = EEG_SC_l##L##_nu##N##_NCOEF, D = (L + 1) * (L + 1);                                           \
+    static __device__ __forceinline__ void run(const xreg* __restrict__ x, const float4* __restrict__ T4, float* __restrict__ out, \
+                                               int ostride = 0, int64_t vstride = 0, bool ok0 = true, bool ok1 = true) {      \
+      SC_DECL                                                                                                                \
+      EEG_SC_l##L##_nu##N##_PROGRAM                                                                                          \
+    }                                                                                                                        \
+  };
+EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
 
 #if EEG_SC_V_ASYNC
 static_assert(EEG_SC_V_PACKED && NPT == 2 && CH == 4, "async variant: packed node pairs, 4 channels per CTA");
@@ -139,10 +133,10 @@ __device__ __forceinline__ void prefetch_tile(float* xs, const float* __restrict
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
-template <int LMAX>
+template <int LMAX, int NU>
 __global__ void __launch_bounds__(THREADS, EEG_SC_V_MINB) k_sym_contract(const float* __restrict__ xg, const float* __restrict__ T,
                                                              float* __restrict__ outg, int64_t N, int C, int tiles_per_cta) {
-  using F = Prog<LMAX>;
+  using F = Prog<LMAX, NU>;
   constexpr int D = F::D, NCOEF = F::NCOEF;
   extern __shared__ __align__(16) float smem[];
   float* Ts = smem;                 // [CH][NCOEF]
@@ -176,10 +170,10 @@ __global__ void __launch_bounds__(THREADS, EEG_SC_V_MINB) k_sym_contract(const f
 #define SC_SMEM_FLOATS(F) (CH * F::NCOEF + CH * (F::D * NT + XPAD))
 #else
 #define SC_SMEM_FLOATS(F) (CH * F::NCOEF + CH * F::D * NT)
-template <int LMAX>
+template <int LMAX, int NU>
 __global__ void __launch_bounds__(THREADS, EEG_SC_V_MINB) k_sym_contract(const float* __restrict__ xg, const float* __restrict__ T,
                                                              float* __restrict__ outg, int64_t N, int C, int tiles_per_cta) {
-  using F = Prog<LMAX>;
+  using F = Prog<LMAX, NU>;
   constexpr int D = F::D, NCOEF = F::NCOEF;
   extern __shared__ __align__(16) float smem[];
   float* Ts = smem;                 // [CH][NCOEF]
@@ -248,13 +242,13 @@ __global__ void __launch_bounds__(THREADS, EEG_SC_V_MINB) k_sym_contract(const f
 
 #endif  // EEG_SC_V_ASYNC
 
-template <int LMAX>
+template <int LMAX, int NU>
 int launch_sc(int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s) {
-  using F = Prog<LMAX>;
+  using F = Prog<LMAX, NU>;
   const size_t smem = (size_t)SC_SMEM_FLOATS(F) * sizeof(float);
   static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_sym_contract<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_sym_contract<LMAX, NU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
       eeg_set_error("eeg_sym_contract_fwd: cannot opt in to %zu B shared memory: %s", smem, cudaGetErrorString(e));
       return 2;
@@ -269,7 +263,7 @@ int launch_sc(int C, const float* x, const float* T, float* out, int64_t N, cuda
   const int tiles_per_cta = (int)((n_tiles + slices - 1) / slices);
   slices = (int)((n_tiles + tiles_per_cta - 1) / tiles_per_cta);
   dim3 grid(groups, slices);
-  k_sym_contract<LMAX><<<grid, THREADS, smem, s>>>(x, T, out, N, C, tiles_per_cta);
+  k_sym_contract<LMAX, NU><<<grid, THREADS, smem, s>>>(x, T, out, N, C, tiles_per_cta);
   EEG_CHECK_LAUNCH("eeg_sym_contract_fwd");
   return 0;
 }
@@ -278,13 +272,15 @@ int launch_sc(int C, const float* x, const float* T, float* out, int64_t N, cuda
 
 #define EEG_SC_CAT2(a, b) a##b
 #define EEG_SC_CAT(a, b) EEG_SC_CAT2(a, b)
-int EEG_SC_CAT(eeg_sc_launch_, EEG_SC_V_NAME)(int lmax, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s) {
+int EEG_SC_CAT(eeg_sc_launch_, EEG_SC_V_NAME)(int lmax, int nu, int C, const float* x, const float* T, float* out, int64_t N, cudaStream_t s) {
   if (C % CH != 0) {
     eeg_set_error("eeg_sym_contract_fwd: C must be a multiple of %d", CH);
     return 1;
   }
-  if (lmax == 4) return launch_sc<4>(C, x, T, out, N, s);
-  if (lmax == 3) return launch_sc<3>(C, x, T, out, N, s);
-  eeg_set_error("eeg_sym_contract_fwd: unsupported lmax=%d", lmax);
+#define EEG_X(L, NN) \
+  if (lmax == L && nu == NN) return launch_sc<L, NN>(C, x, T, out, N, s);
+  EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
+  eeg_set_error("eeg_sym_contract_fwd: unsupported (lmax=%d, correlation=%d)", lmax, nu);
   return 1;
 }

@@ -10,8 +10,7 @@
 //   eeg_sc_coefficients_bwd: dW[k,c] = sum_slot A[slot,k] sum_z dT[z][slot][c]   (transpose of eeg_sc_coefficients); the
 //                            slices are first summed into slice 0 in place (dT is scratch)
 #include "eeg_common.cuh"
-#include "generated/scw_l3_nu3.cuh"
-#include "generated/scw_l4_nu3.cuh"
+#include "generated/all_scw.cuh"
 
 namespace {
 
@@ -20,9 +19,11 @@ namespace {
 // stalls).  The WG_WPS warps of a segment take the nodes of a tile round robin and are summed through shared memory at the end.
 constexpr int WG_SEGS = 4, WG_WPS = 2, WG_WARPS = WG_SEGS * WG_WPS, WG_NB = 4 * WG_WPS, WG_SLICES = 74;
 
-template <int LMAX> struct Scw;
-template <> struct Scw<3> { static constexpr int SEG = EEG_SCW_l3_nu3_SEG, NSEG = EEG_SCW_l3_nu3_NSEG, NCOEF = EEG_SCW_l3_nu3_NCOEF; };
-template <> struct Scw<4> { static constexpr int SEG = EEG_SCW_l4_nu3_SEG, NSEG = EEG_SCW_l4_nu3_NSEG, NCOEF = EEG_SCW_l4_nu3_NCOEF; };
+template <int LMAX, int NU> struct Scw;
+#define EEG_X(L, N) \
+  template <> struct Scw<L, N> { static constexpr int SEG = EEG_SCW_l##L##_nu##N##_SEG, NSEG = EEG_SCW_l##L##_nu##N##_NSEG, NCOEF = EEG_SCW_l##L##_nu##N##_NCOEF; };
+EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
 
 __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, bool valid) {
   const unsigned dst = (unsigned)__cvta_generic_to_shared(smem);
@@ -40,10 +41,10 @@ __device__ __forceinline__ void cp_async16_zfill(void* smem, const void* gmem, b
     BODY                                                    \
   }
 
-template <int LMAX>
+template <int LMAX, int NU>
 __global__ void __launch_bounds__(WG_WARPS * 32, 1) k_sc_wgrad(const float* __restrict__ x, const float* __restrict__ dout, int C,
                                                                 int64_t N, float* __restrict__ dT) {
-  constexpr int D = (LMAX + 1) * (LMAX + 1), SEG = Scw<LMAX>::SEG, NCOEF = Scw<LMAX>::NCOEF;
+  constexpr int D = (LMAX + 1) * (LMAX + 1), SEG = Scw<LMAX, NU>::SEG, NCOEF = Scw<LMAX, NU>::NCOEF;
   constexpr int TILE = WG_NB * D * 32;                 // floats per tensor per stage
   extern __shared__ __align__(16) float wg_smem[];     // [2 stages][x | dout][WG_NB][D][32]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -78,11 +79,10 @@ __global__ void __launch_bounds__(WG_WARPS * 32, 1) k_sc_wgrad(const float* __re
     __syncthreads();
     const float* xt = wg_smem + (t & 1) * 2 * TILE + lane;
     const float* gt = xt + TILE;
-    if constexpr (LMAX == 4) {
-      EEG_SCW_l4_nu3_SWITCH(seg, WG_LOOP)
-    } else {
-      EEG_SCW_l3_nu3_SWITCH(seg, WG_LOOP)
-    }
+#define EEG_X(L, N) \
+    if constexpr (LMAX == L && NU == N) { EEG_SCW_l##L##_nu##N##_SWITCH(seg, WG_LOOP) }
+    EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
     __syncthreads();   // the stage is refilled by the next iteration's prefetch
   }
   // fold the WG_WPS partial sums of a segment (fixed order), staging memory reused: [WG_SEGS][SEG][32]
@@ -132,22 +132,22 @@ __global__ void k_sc_coefficients_bwd(const int32_t* __restrict__ tp, const int3
   }
 }
 
-template <int LMAX>
+template <int LMAX, int NU>
 int launch_wgrad(int C, const float* x, const float* dout, int64_t N, float* dT, cudaStream_t s) {
   constexpr int D = (LMAX + 1) * (LMAX + 1);
   constexpr size_t smem = (size_t)2 * 2 * WG_NB * D * 32 * sizeof(float);
   static EegDevFlags attr_dev; bool& attr = eeg_dev_flag(attr_dev);
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k_sc_wgrad<LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_sc_wgrad<LMAX, NU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
       eeg_set_error("eeg_sc_coef_grad: cannot opt in to %zu B shared memory: %s", smem, cudaGetErrorString(e));
       return 2;
     }
     attr = true;
   }
-  static_assert(Scw<LMAX>::NSEG % WG_SEGS == 0, "segment count");
-  dim3 grid(Scw<LMAX>::NSEG / WG_SEGS, C / 32, WG_SLICES);   // N == 0: every slice is written as zeros
-  k_sc_wgrad<LMAX><<<grid, WG_WARPS * 32, smem, s>>>(x, dout, C, N, dT);
+  static_assert(Scw<LMAX, NU>::NSEG % WG_SEGS == 0, "segment count");
+  dim3 grid(Scw<LMAX, NU>::NSEG / WG_SEGS, C / 32, WG_SLICES);   // N == 0: every slice is written as zeros
+  k_sc_wgrad<LMAX, NU><<<grid, WG_WARPS * 32, smem, s>>>(x, dout, C, N, dT);
   EEG_CHECK_LAUNCH("eeg_sc_coef_grad");
   return 0;
 }
@@ -158,10 +158,17 @@ extern "C" int eeg_sc_grad_slices(void) { return WG_SLICES; }
 
 extern "C" int eeg_sc_coef_grad(int lmax, int nu, int C, const float* x, const float* dout, int n_coef, int64_t N, float* dT,
                                 void* stream) {
-  EEG_REQUIRE(nu == 3 && (lmax == 3 || lmax == 4), "eeg_sc_coef_grad: unsupported (lmax=%d, correlation=%d)", lmax, nu);
+  EEG_REQUIRE(nu >= 1 && nu <= 3 && lmax >= 1 && lmax <= 4, "eeg_sc_coef_grad: unsupported (lmax=%d, correlation=%d)", lmax, nu);
   EEG_REQUIRE(C > 0 && C % 32 == 0, "eeg_sc_coef_grad: C must be a multiple of 32");
-  EEG_REQUIRE(n_coef == (lmax == 4 ? Scw<4>::NCOEF : Scw<3>::NCOEF), "eeg_sc_coef_grad: n_coef %d does not match the generated program", n_coef);
-  return lmax == 4 ? launch_wgrad<4>(C, x, dout, N, dT, (cudaStream_t)stream) : launch_wgrad<3>(C, x, dout, N, dT, (cudaStream_t)stream);
+#define EEG_X(L, NN)                                                                                                               \
+  if (lmax == L && nu == NN) {                                                                                                     \
+    constexpr int want = Scw<L, NN>::NCOEF;                                                                                        \
+    EEG_REQUIRE(n_coef == want, "eeg_sc_coef_grad: n_coef %d does not match the generated program", n_coef);                       \
+    return launch_wgrad<L, NN>(C, x, dout, N, dT, (cudaStream_t)stream);                                                           \
+  }
+  EEG_SC_COMBOS(EEG_X)
+#undef EEG_X
+  return 1;
 }
 
 extern "C" int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_row, const float* t_val, int n_wrows, int n_coef,

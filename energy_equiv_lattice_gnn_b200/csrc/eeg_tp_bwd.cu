@@ -7,14 +7,8 @@
 // G_p[i,k] = sum_j C_p[i,j,k] Y_j are staged once per warp in shared memory (the forward's table), then a generated
 // straight-line function (tools/gen_kernels.py: gen_tp2_bwd) evaluates every path.
 #include "eeg_common.cuh"
-#include "generated/tp2_0_3.cuh"
-#include "generated/tp2_0_4.cuh"
-#include "generated/tp2_3_3.cuh"
-#include "generated/tp2_4_4.cuh"
-#include "generated/tp2b_0_3.cuh"
-#include "generated/tp2b_0_4.cuh"
-#include "generated/tp2b_3_3.cuh"
-#include "generated/tp2b_4_4.cuh"
+#include "generated/all_tp2.cuh"
+#include "generated/all_tp2b.cuh"
 
 namespace {
 
@@ -33,7 +27,7 @@ struct TpB;
       eeg_tp2b_##LIN##_##LMAX(x, G4, wp, ws, dMp, cs, dwp, dx);                                                     \
     }                                                                                                               \
   };
-EEG_TPB(0, 3) EEG_TPB(0, 4) EEG_TPB(3, 3) EEG_TPB(4, 4)
+EEG_TP_COMBOS(EEG_TPB)
 #undef EEG_TPB
 
 template <int LIN, int LMAX>
@@ -150,10 +144,10 @@ extern "C" int eeg_tp_scatter_bwd(int lmax_in, int lmax, int C, const float* h, 
   if (N == 0 || E == 0) return 0;
   EEG_REQUIRE(ystride % 4 == 0 && ystride <= 32, "eeg_tp_scatter_bwd: ystride must be a multiple of 4 and <= 32 (got %d)", ystride);
   cudaStream_t s = (cudaStream_t)stream;
-  if (lmax_in == 0 && lmax == 3) return launch_tpb<0, 3>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
-  if (lmax_in == 3 && lmax == 3) return launch_tpb<3, 3>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
-  if (lmax_in == 0 && lmax == 4) return launch_tpb<0, 4>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
-  if (lmax_in == 4 && lmax == 4) return launch_tpb<4, 4>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
+#define EEG_X(LIN, LMAX) \
+  if (lmax_in == LIN && lmax == LMAX) return launch_tpb<LIN, LMAX>(h, Y, ystride, w_t, E, sender_sorted, row_ptr, inv_norm, dM, dw, dh, N, C, s);
+  EEG_TP_COMBOS(EEG_X)
+#undef EEG_X
   eeg_set_error("eeg_tp_scatter_bwd: unsupported (lmax_in=%d, lmax=%d)", lmax_in, lmax);
   return 1;
 }

@@ -56,8 +56,13 @@ class EnergyEquivGNN(torch.nn.Module):
             raise ValueError(f"Unknown positive function: {params.positive_function}")
         if params.global_reduction not in ("mean", "sum"):
             raise ValueError(f"Unknown global reduction: {params.global_reduction}")
-        if int(params.inter_MLP_dim) != 64 or int(params.inter_MLP_layers) < 2 or 2 * int(params.num_edge_bases) > 16:
-            raise NotImplementedError("radial MLP kernel: inter_MLP_dim must be 64, inter_MLP_layers >= 2, 2*num_edge_bases <= 16")
+        if not 1 <= lmax <= 4:
+            raise NotImplementedError(f"lmax must be in 1..4 (generated kernels, tools/gen_kernels.py); got {lmax}")
+        if not 1 <= int(params.correlation) <= 3:
+            raise NotImplementedError(f"correlation must be in 1..3 (generated kernels); got {params.correlation}")
+        if int(params.inter_MLP_layers) < 1 or int(params.inter_MLP_dim) % 4 != 0 or int(params.num_edge_bases) < 2 or \
+                int(params.num_edge_bases) % 2 != 0:
+            raise NotImplementedError("radial MLP: inter_MLP_layers >= 1, inter_MLP_dim a multiple of 4, num_edge_bases even and >= 2")
         self.correlation = int(params.correlation)
         self.number_of_edge_basis = nb = int(params.num_edge_bases)
         self.max_edge_radius = float(params.max_edge_radius)
@@ -84,7 +89,7 @@ class EnergyEquivGNN(torch.nn.Module):
             wnum = len(plan["paths"]) * C
             last = torch.nn.Linear(H, wnum, bias=False)
             torch.nn.init.xavier_uniform_(last.weight, gain=10)
-            mods = [torch.nn.Linear(2 * nb, H), torch.nn.SiLU()]
+            mods = [torch.nn.Linear(2 * nb, H), torch.nn.SiLU()]   # gnn/blocks.py:541-548: inter_MLP_layers <= 2 gives two linears
             for _ in range(nl - 2):
                 mods += [torch.nn.Linear(H, H), torch.nn.SiLU()]
             mods.append(last)
@@ -250,8 +255,17 @@ class EnergyEquivGNN(torch.nn.Module):
             # radial MLP (gnn/blocks.py:538-549,590): fused, last layers on tcgen05; output path-major w_t[P*C/32, E, 32]
             lins = [m for m in inter.conv_tp_weights if isinstance(m, torch.nn.Linear)]
             nv.set_tag(f'L{i}.radial_mlp')
-            img, bh = self._radial_image(i, lins)
-            w = nv.radial_mlp(f, lins[0].weight.detach(), lins[0].bias.detach(), bh, len(lins) - 2, img, lins[-1].weight.shape[0])
+            if nv.radial_supported(f.shape[1], int(self.params.inter_MLP_dim), len(lins)):
+                img, bh = self._radial_image(i, lins)
+                w = nv.radial_mlp(f, lins[0].weight.detach(), lins[0].bias.detach(), bh, len(lins) - 2, img, lins[-1].weight.shape[0])
+            else:   # any other width / depth: layer-by-layer block linears (tcgen05 for K >= 128) + SiLU, then the path-major layout
+                a, lay_in = f, self._lay_f
+                for lin in lins[:-1]:
+                    a = nv.silu_fwd(nv.block_linear(a, lay_in, lin.weight.detach().reshape(-1), [0], [1.0], self._lay_mlp, E,
+                                                    bias=lin.bias.detach(), transB=True))
+                    lay_in = self._lay_mlp
+                w = nv.to_path_major(nv.block_linear(a, lay_in, lins[-1].weight.detach().reshape(-1), [0], [1.0], self._lay_w[i], E, transB=True),
+                                     lins[-1].weight.shape[0])
             acts = None
             plan = self._tp[i]
             nv.set_tag(f'L{i}.tp_scatter')

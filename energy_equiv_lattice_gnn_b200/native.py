@@ -24,7 +24,7 @@ SYMBOLS = [
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
     "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
     "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd", "eeg_segment_sum_rows",
-    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd",
+    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd", "eeg_blocks32_transpose",
 ]
 
 
@@ -264,6 +264,21 @@ def radial_mlp(f, W0, b0, bh, n_hidden, img, n_out):
                                     C.c_int(W0.shape[0]), _p(img, f32), C.c_int(n_out), _p(w_t), C.c_int64(E), _stream()),
            "eeg_radial_mlp_fwd")
     return w_t
+
+
+def radial_supported(n_in: int, hidden_dim: int, n_linear: int) -> bool:
+    """Shape domain of the fused tcgen05 radial MLP (eeg_radial_mlp_fwd): inter_MLP_dim 64, >= 2 linears, <= 16 inputs."""
+    return hidden_dim == 64 and 2 <= n_linear <= 6 and 0 < n_in <= 16
+
+
+def to_path_major(w_edge_major, n_out: int):
+    """[E, n_out] -> w_t [n_out/32, E, 32]"""
+    E = w_edge_major.shape[0]
+    out = torch.empty(n_out // 32, E, 32, dtype=f32, device=w_edge_major.device)
+    _begin("eeg_blocks32_transpose")
+    _check(lib().eeg_blocks32_transpose(_p(w_edge_major, f32), _p(out), C.c_int64(E), C.c_int(n_out // 32), C.c_int(1), _stream()),
+           "eeg_blocks32_transpose")
+    return out
 
 
 def tp_scatter(lmax_in, lmax, Cch, h, Y, w_t, sender_sorted, row_ptr, inv_norm, rows_total, n_nodes, umma: bool = False):

@@ -231,6 +231,10 @@ int eeg_collate_gather(const float* pos, const float* node_attrs, const int32_t*
  * Q = Ry(alpha) Rx(beta) Ry(gamma); counter-based generator: lattice g of the call uses counters 3*(offset+g) .. +2. */
 int eeg_rand_rotations(uint64_t seed, uint64_t offset, int64_t G, float* Q /*[G,3,3]*/, void* stream);
 
+/* [E, B, 32] <-> [B, E, 32] (to_path_major = 1 / 0): edge-major per-edge weights of a generic radial MLP <-> the path-major
+ * w_t layout of eeg_tp_scatter_fwd (used when conv_tp_weights is outside eeg_radial_mlp_fwd's fused shape). */
+int eeg_blocks32_transpose(const float* in, float* out, int64_t E, int B, int to_path_major, void* stream);
+
 /* ---- RadialEmbeddingBlock (gnn/blocks.py:89-102): BesselBasis (gnn/mace.py:28-71) x PolynomialCutoff (gnn/mace.py:74-106).
  * edge_lengths [E] -> out [E, num_bessel].  Defined by the reference, not used by EnergyEquivGNN. */
 int eeg_radial_embedding_fwd(const float* edge_lengths, int64_t E, int num_bessel, float r_max, int num_polynomial_cutoff,
