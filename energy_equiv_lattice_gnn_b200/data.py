@@ -233,11 +233,15 @@ class RotateLat:
     'cartesian_4', gnn/datasets.py:256-269) and returns a new `Batch` with rotated `positions` / `shifts` and Mandel
     `[G,6,6]` targets.  `Q` is `[G,3,3]` (one rotation per lattice, drawn like `o3.rand_matrix()` when omitted);
     `rotate=False` only converts the targets, and then `Q` must be None, as in the reference (:126-127).
+    `seed` (int) draws the rotations ON THE DEVICE (`eeg_rand_rotations`, counter-based: the stream position advances by G per
+    call, so epochs are reproducible from (seed, number of lattices seen)); `generator` draws them on the host like round 1.
     CUDA only: the kernels live in libeeg_b200 (`eeg_rotate_vec3`, `eeg_rotate_cart4_to_mandel`)."""
 
-    def __init__(self, rotate: bool = True, generator: Optional[torch.Generator] = None):
+    def __init__(self, rotate: bool = True, generator: Optional[torch.Generator] = None, seed: Optional[int] = None):
         self.rotate = rotate
         self.generator = generator
+        self.seed = seed
+        self.offset = 0
 
     def __call__(self, batch: Batch, Q: Optional[torch.Tensor] = None) -> Batch:
         from . import native
@@ -245,7 +249,10 @@ class RotateLat:
         dev = batch.positions.device
         out = Batch(**batch.__dict__)
         if self.rotate:
-            if Q is None:
+            if Q is None and self.seed is not None:
+                Q = native.rand_rotations(int(self.seed), self.offset, G, dev)
+                self.offset += G
+            elif Q is None:
                 Q = rand_rotations(G, self.generator)
             Q = Q.to(device=dev, dtype=torch.float32).contiguous()
             if Q.shape != (G, 3, 3):

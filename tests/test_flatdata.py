@@ -152,3 +152,14 @@ def test_device_rotation_sampling(cuda_device):
     assert float(((Qd ** 2).mean(0) - 1 / 3).abs().max()) < 0.01
     other = native.rand_rotations(8, 0, 100, cuda_device)
     assert not torch.equal(other, Q[:100])
+    # RotateLat(seed=...) consumes that stream: second call continues where the first stopped
+    from energy_equiv_lattice_gnn_b200.data import RotateLat
+    data = [synthetic_lattice(950 + i, 6, with_target=False) for i in range(5)]
+    b = collate(data).to(cuda_device)
+    rot = RotateLat(rotate=True, seed=7)
+    b1, b2 = rot(b), rot(b)
+    assert rot.offset == 10
+    Qs = Q[:10]
+    gid = b.batch
+    assert torch.allclose(b1.positions, torch.einsum("nij,nj->ni", Qs[:5][gid], b.positions), atol=1e-6)
+    assert torch.allclose(b2.positions, torch.einsum("nij,nj->ni", Qs[5:10][gid], b.positions), atol=1e-6)
