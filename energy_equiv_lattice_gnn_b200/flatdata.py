@@ -15,8 +15,9 @@ mapped, uploaded to HBM once (a 10^6-lattice catalogue is a few GB of the 180 GB
     convert_lat(lat_path, out_path)                     `.lat` text -> flat binary (fast parser + process_one), with the
                                                         measured lattices/s
 
-Targets are stored as the 21 upper-triangular... no: as the full Cartesian rank-4 tensors `[81]` (stiffness, compliance),
-exactly what `GLAMM_Dataset.process_one` stores for graph format 'cartesian_4' and what `RotateLat` consumes.
+Targets are stored as the full Cartesian rank-4 tensors `[81]` (stiffness, compliance): what `GLAMM_Dataset.process_one`
+stores for graph format 'cartesian_4' and what `RotateLat` consumes.  Throughput: tools/flatdata_bench.py
+(profiles/r02_flatdata_throughput.json).
 """
 from __future__ import annotations
 
@@ -155,18 +156,19 @@ class FlatDataset:
             for k in present:
                 setattr(out, k, g0 if k == first else a[k].index_select(0, idx_d))
         else:
-            # host collation (the reference's own DataLoader path), vectorised: repeat-interleave of the offsets
+            # host collation (the reference's own DataLoader path), vectorised in numpy: repeat-interleave of the offsets
             gid_n = np.repeat(np.arange(G), np.diff(meta[2]))
             gid_e = np.repeat(np.arange(G), np.diff(meta[3]))
-            src_n = torch.from_numpy(meta[0, gid_n] + (np.arange(N) - meta[2, gid_n]))
-            src_e = torch.from_numpy(meta[1, gid_e] + (np.arange(E) - meta[3, gid_e]))
-            noff = torch.from_numpy(meta[2, gid_e])
-            ei = torch.stack([a["edge_snd"][src_e].long() + noff, a["edge_rcv"][src_e].long() + noff])
-            out = Batch(positions=a["positions"][src_n], node_attrs=a["node_attrs"][src_n].reshape(-1, 1), edge_index=ei,
-                        shifts=a["shifts"][src_e], edge_attr=a["edge_attr"][src_e].reshape(-1, 1), batch=torch.from_numpy(gid_n),
-                        num_graphs=G)
+            src_n = meta[0, gid_n] + (np.arange(N) - meta[2, gid_n])
+            src_e = meta[1, gid_e] + (np.arange(E) - meta[3, gid_e])
+            noff = meta[2, gid_e]
+            h = {k: v.numpy() for k, v in a.items()}
+            ei = np.stack([h["edge_snd"][src_e].astype(np.int64) + noff, h["edge_rcv"][src_e].astype(np.int64) + noff])
+            out = Batch(positions=torch.from_numpy(h["positions"][src_n]), node_attrs=torch.from_numpy(h["node_attrs"][src_n]).reshape(-1, 1),
+                        edge_index=torch.from_numpy(ei), shifts=torch.from_numpy(h["shifts"][src_e]),
+                        edge_attr=torch.from_numpy(h["edge_attr"][src_e]).reshape(-1, 1), batch=torch.from_numpy(gid_n), num_graphs=G)
             for k in present:
-                setattr(out, k, a[k][torch.from_numpy(idx)])
+                setattr(out, k, torch.from_numpy(h[k][idx]))
         for k in present:   # Cartesian rank-4 targets keep the reference's [G,3,3,3,3] shape
             t = getattr(out, k)
             if t.shape[1] == 81:
