@@ -30,6 +30,11 @@ struct TpB;
 EEG_TP_COMBOS(EEG_TPB)
 #undef EEG_TPB
 
+// Software prefetch into L1 (no registers, no shared memory): the generated per-edge program issues ~300 dependent global
+// loads (230 dM rows, 42 weight rows, 25 sender rows) between ~2000 FMAs and ran at 72 % long-scoreboard stalls
+// (profiles/r01_ncu_tp_bwd_summary.txt); the lines of the NEXT edge / node are requested while the current one is evaluated.
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 template <int LIN, int LMAX>
 __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
                                                        const float* __restrict__ w_t, int64_t E, const int32_t* __restrict__ sender,
@@ -50,11 +55,24 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__
   const int c = chunk * 32 + lane;
   const int64_t wstride = (int64_t)chunks * E * 32;   // floats between consecutive paths of w_t
   int ee = __ldg(row_ptr + n0);
+  const int e_last = __ldg(row_ptr + n1);
+  const float* const wbase = w_t + (int64_t)chunk * E * 32;
+  auto prefetch_edge = [&](int e) {   // weight rows (one 128-byte line per path) and sender rows of CSR slot e
+    for (int p = lane; p < I::NPATHS; p += 32) prefetch_l1(wbase + (int64_t)p * wstride + (int64_t)e * 32);
+    if (lane < DIN) prefetch_l1(h + ((int64_t)__ldg(sender + e) * DIN + lane) * C + chunk * 32);
+  };
+  auto prefetch_node = [&](int64_t n) {   // the node's dM rows for this 32-channel chunk
+    const float* base = dM + n * (int64_t)I::ROWS * C + chunk * 32;
+    for (int r = lane; r < I::ROWS; r += 32) prefetch_l1(base + (int64_t)r * C);
+  };
+  if (ee < e_last) prefetch_edge(ee);
   for (int64_t n = n0; n < n1; ++n) {
     const int eb = ee;
     ee = __ldg(row_ptr + n + 1);
+    if (n + 1 < n1) prefetch_node(n + 1);
     const float* dMp = dM + n * (int64_t)I::ROWS * C + c;
     for (int e = eb; e < ee; ++e) {
+      if (e + 1 < e_last) prefetch_edge(e + 1);
       const int s = __ldg(sender + e);
       const float yv = lane < ystride ? __ldg(Y + (int64_t)e * ystride + lane) : 0.f;
       __syncwarp();
