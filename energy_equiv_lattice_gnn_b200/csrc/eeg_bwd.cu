@@ -13,7 +13,7 @@
 namespace {
 
 // ------------------------------------------------------------------------------------------------ linear weight gradient
-constexpr int WG_ROWS = 4096;   // rows per CTA
+constexpr int WG_ROWS_MAX = 4096;   // rows per CTA (upper bound; see wg_rows_per_cta)
 
 struct WgBlock {
   int rows, k, nout, in_off, in_ld, out_off;
@@ -24,7 +24,24 @@ struct WgBlock {
 struct WgParams {
   WgBlock b[EEG_MAX_L];
   int n_blocks, in_stride, out_stride, transB;
+  int wg_rows;   // rows per CTA
 };
+
+// Rows per CTA: enough row slices that the grid holds >= ~4 CTAs per SM (the K = 32 -> 32 linears have ONE 32 x 32 tile per
+// irrep block: with 4096 rows per CTA their weight gradients ran on 94 CTAs at 0.8 TB/s), multiple of 32, at most WG_ROWS_MAX.
+static int wg_rows_per_cta(const EegLayout* lin, const EegLayout* lout, const int32_t* k_override, int64_t N) {
+  int64_t rows_tiles = 0;   // sum over blocks of rows * tiles
+  for (int b = 0; b < lin->n_blocks; ++b) {
+    const int k = k_override ? k_override[b] : lin->mul[b], n = lout ? lout->mul[b] : 32;
+    if (k <= 0 || n <= 0) continue;
+    rows_tiles += N * lin->rows[b] * (int64_t)((k + 31) / 32) * ((n + 31) / 32);
+  }
+  int64_t r = rows_tiles / (4 * EEG_NUM_SMS);
+  r = (r + 31) / 32 * 32;
+  if (r < 256) r = 256;
+  if (r > WG_ROWS_MAX) r = WG_ROWS_MAX;
+  return (int)r;
+}
 
 // ws != nullptr: deterministic mode - the row slice `cta / tiles` of a tile writes its partial sums to
 // ws[slice * ws_stride + element] (bias partials behind the weights at n_weights + column) and k_wgrad_reduce adds the
@@ -42,8 +59,8 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
   cta -= d.cta_begin;
   const int tiles = d.ktiles * d.ntiles;
   const int kt = (cta % tiles) / d.ntiles, nt = (cta % tiles) % d.ntiles;
-  const int64_t r_begin = (int64_t)(cta / tiles) * WG_ROWS, total = N * d.rows;
-  const int64_t r_end = r_begin + WG_ROWS < total ? r_begin + WG_ROWS : total;
+  const int64_t r_begin = (int64_t)(cta / tiles) * P.wg_rows, total = N * d.rows;
+  const int64_t r_end = r_begin + P.wg_rows < total ? r_begin + P.wg_rows : total;
   const int t = threadIdx.x, tk = t >> 3, tn = t & 7;   // thread: k = 2 tk + {0,1}, n = 4 tn + {0..3}
   const int lr = t >> 2, lq = t & 3;                     // loader: row lr, float4 columns lq and lq + 4
   float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
@@ -111,7 +128,7 @@ __global__ void k_wgrad_reduce(const float* __restrict__ ws, int64_t ws_stride, 
     for (int q = 0; q < P.n_blocks; ++q)
       if (P.b[q].k > 0 && P.b[q].nout > 0 && i >= P.b[q].w_off && i < P.b[q].w_off + (int64_t)P.b[q].k * P.b[q].nout) b = q;
   if (b < 0) return;
-  const int64_t slices = (N * P.b[b].rows + WG_ROWS - 1) / WG_ROWS;
+  const int64_t slices = (N * P.b[b].rows + P.wg_rows - 1) / P.wg_rows;
   float s = 0.f;
   for (int64_t sl = 0; sl < slices; ++sl) s += ws[sl * ws_stride + i];
   if (i >= n_weights) dbias[i - n_weights] += s;
@@ -393,6 +410,7 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
   P.in_stride = lin->stride;
   P.out_stride = lout->stride;
   P.transB = transB;
+  P.wg_rows = wg_rows_per_cta(lin, lout, k_override, N);
   int64_t ctas = 0;
   for (int b = 0; b < P.n_blocks; ++b) {
     EEG_REQUIRE(lin->rows[b] == lout->rows[b], "eeg_block_linear_wgrad: block %d rows differ", b);
@@ -411,7 +429,7 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
     d.cta_begin = (int)ctas;
     d.ktiles = (d.k + 31) / 32;
     d.ntiles = (d.nout + 31) / 32;
-    const int64_t chunks = (N * d.rows + WG_ROWS - 1) / WG_ROWS;
+    const int64_t chunks = (N * d.rows + P.wg_rows - 1) / P.wg_rows;
     ctas += (d.k > 0 && d.nout > 0) ? chunks * d.ktiles * d.ntiles : 0;
     if (d.k == 0 || d.nout == 0) { d.ktiles = 1; d.ntiles = 1; }
     EEG_REQUIRE(ctas < (1LL << 31), "eeg_block_linear_wgrad: too many tiles");
@@ -422,7 +440,7 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
   if (ws != nullptr) {
     int64_t slices = 0;
     for (int b = 0; b < P.n_blocks; ++b) {
-      const int64_t sl = (N * P.b[b].rows + WG_ROWS - 1) / WG_ROWS;
+      const int64_t sl = (N * P.b[b].rows + P.wg_rows - 1) / P.wg_rows;
       if (P.b[b].k > 0 && P.b[b].nout > 0 && sl > slices) slices = sl;
       EEG_REQUIRE(P.b[b].k == 0 || P.b[b].nout == 0 || P.b[b].w_off + (int64_t)P.b[b].k * P.b[b].nout <= n_weights,
                   "eeg_block_linear_wgrad: block %d exceeds n_weights", b);
@@ -440,10 +458,12 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
 }
 
 // floats of workspace eeg_block_linear_wgrad needs in deterministic mode
-extern "C" int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, int64_t n_weights, int bias_cols, int64_t N) {
+extern "C" int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t n_weights, int bias_cols,
+                                                    int64_t N) {
   int64_t slices = 0;
+  const int wg_rows = lin ? wg_rows_per_cta(lin, lout, nullptr, N) : WG_ROWS_MAX;
   for (int b = 0; lin && b < lin->n_blocks; ++b) {
-    const int64_t sl = (N * lin->rows[b] + WG_ROWS - 1) / WG_ROWS;
+    const int64_t sl = (N * lin->rows[b] + wg_rows - 1) / wg_rows;
     if (sl > slices) slices = sl;
   }
   return slices * (n_weights + bias_cols);

@@ -352,7 +352,7 @@ def linear_wgrad(x, lin: EegLayout, dy, lout: EegLayout, w_off, scale, n_weights
     db = torch.zeros(want_bias, dtype=f32, device=x.device) if want_bias else None
     L = lib()
     L.eeg_block_linear_wgrad_ws_floats.restype = C.c_int64
-    nws = int(L.eeg_block_linear_wgrad_ws_floats(C.byref(lin), C.c_int64(n_weights), C.c_int(want_bias), C.c_int64(n_rows)))
+    nws = int(L.eeg_block_linear_wgrad_ws_floats(C.byref(lin), C.byref(lout), C.c_int64(n_weights), C.c_int(want_bias), C.c_int64(n_rows)))
     ws = torch.empty(max(nws, 1), dtype=f32, device=x.device)   # deterministic mode: row slices are added in fixed order
     _begin("eeg_block_linear_wgrad")
     _check(L.eeg_block_linear_wgrad(_p(x, f32), C.byref(lin), _p(dy, f32), C.byref(lout), _arr(C.c_int64, w_off), _arr(C.c_float, scale, fill=0.0),

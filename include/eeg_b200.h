@@ -130,13 +130,13 @@ int eeg_pool_tail_fwd(const float* o, const EegLayout* lo, const int32_t* graph_
 
 /* dW_b[u,w] += scale_b * sum_{n,m} x[n,b,m,u] dy[n,b,m,w]  (transB = 1: stored as dW_b[w,u], torch.nn.Linear layout);
  * dbias[w] += sum_n dy[n,0,0,w] (may be NULL).  in_ld / k_override may be NULL (row stride / K = mul of the layout).
- * n_weights = floats of dW.  ws: workspace of eeg_block_linear_wgrad_ws_floats(lin, n_weights, bias columns, N) floats ->
+ * n_weights = floats of dW.  ws: workspace of eeg_block_linear_wgrad_ws_floats(lin, lout, n_weights, bias columns, N) floats ->
  * DETERMINISTIC (row slices are written to ws and added in slice order); ws NULL -> atomicAdd per slice (order varies). */
 int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
                            const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
                            const int32_t* k_override, float* dW, float* dbias, int64_t N, int64_t n_weights, float* ws,
                            int64_t ws_floats, void* stream);
-int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, int64_t n_weights, int bias_cols, int64_t N);
+int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t n_weights, int bias_cols, int64_t N);
 /* out[c] += sum_r row_scale[r] * x[r*ld + c]   (row_scale may be NULL = 1): bias / embedding gradients.
  * ws: ceil(R / 256) * cols floats -> deterministic (CTA partials added in order); NULL -> atomicAdd. */
 int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,
