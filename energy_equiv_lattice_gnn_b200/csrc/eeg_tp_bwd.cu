@@ -6,6 +6,7 @@
 // One warp per run of 16 receiver rows (contiguous CSR edges), lane = channel; per edge the lane-uniform matrices
 // G_p[i,k] = sum_j C_p[i,j,k] Y_j are staged once per warp in shared memory (the forward's table), then a generated
 // straight-line function (tools/gen_kernels.py: gen_tp2_bwd) evaluates every path.
+#include <stdlib.h>
 #include "eeg_common.cuh"
 #include "generated/all_tp2.cuh"
 #include "generated/all_tp2b.cuh"
@@ -23,8 +24,8 @@ struct TpB;
                          NPATHS = EEG_TP2_##LIN##_##LMAX##_NPATHS;                                                  \
     static __device__ __forceinline__ const int4* tab() { return eeg_tp2_##LIN##_##LMAX##_tab; }                    \
     static __device__ __forceinline__ void run(const float* x, const float4* G4, const float* wp, long ws, const float* dMp, \
-                                               long cs, float* dwp, float* dx) {                                    \
-      eeg_tp2b_##LIN##_##LMAX(x, G4, wp, ws, dMp, cs, dwp, dx);                                                     \
+                                               long ms, long cs, float* dwp, float* dx) {                           \
+      eeg_tp2b_##LIN##_##LMAX(x, G4, wp, ws, dMp, ms, cs, dwp, dx);                                                 \
     }                                                                                                               \
   };
 EEG_TP_COMBOS(EEG_TPB)
@@ -90,7 +91,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__
       }
       __syncwarp();
       float* dwp = dw + (int64_t)e * I::NPATHS * C + c;
-      I::run(x, reinterpret_cast<const float4*>(Gs), w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane, wstride, dMp, C, dwp, dx);
+      I::run(x, reinterpret_cast<const float4*>(Gs), w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane, wstride, dMp, C, C, dwp, dx);
       // fold 1 / agg_norm_const (callers that pre-scale dM pass inv_norm = 1 and skip the read-modify-write of dw)
       if (inv_norm != 1.0f) {
 #pragma unroll
@@ -102,14 +103,97 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd(const float* __restrict__
   }
 }
 
+
+// ---- variant 2 (default): the 4 warps of a CTA share ONE receiver node at a time.  The node's dM rows (ROWS x 32 floats of
+// this channel chunk, 29 KB for lmax 4) are staged in shared memory by cp.async, double buffered across nodes, and every
+// warp evaluates a different edge of the node from that tile: 230 of the ~300 loads per edge become LDS instead of global
+// loads that 16 resident warps evicted from L1 before use (variant 1: 72 % long-scoreboard stalls, an L1 prefetch did not help).
+constexpr int NPC2 = 16;   // receiver nodes per CTA
+__device__ __forceinline__ void cp_async16_b(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
+
+template <int LIN, int LMAX>
+__global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
+                                                        const float* __restrict__ w_t, int64_t E, const int32_t* __restrict__ sender,
+                                                        const int32_t* __restrict__ row_ptr, float inv_norm, const float* __restrict__ dM,
+                                                        float* __restrict__ dw, float* __restrict__ dxe, int64_t N, int C, int chunks) {
+  using I = TpB<LIN, LMAX>;
+  constexpr int DIN = (LIN + 1) * (LIN + 1);
+  constexpr int TILE = I::ROWS * 32;   // floats
+  extern __shared__ __align__(16) uint8_t tpb_smem[];
+  int4* tab_s = reinterpret_cast<int4*>(tpb_smem);
+  float* Gall = reinterpret_cast<float*>(tpb_smem + (size_t)I::NTAB * 16);
+  float* dMs = Gall + (size_t)WARPS * I::NTAB;   // [2][ROWS][32]
+  for (int i = threadIdx.x; i < I::NTAB; i += WARPS * 32) tab_s[i] = I::tab()[i];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* Gs = Gall + (size_t)wid * I::NTAB;
+  const int chunk = blockIdx.x % chunks;
+  const int64_t n0 = (int64_t)(blockIdx.x / chunks) * NPC2;
+  if (n0 >= N) return;
+  const int64_t n1 = n0 + NPC2 < N ? n0 + NPC2 : N;
+  const int c = chunk * 32 + lane;
+  const int64_t wstride = (int64_t)chunks * E * 32;
+  auto stage = [&](int64_t n, int buf) {
+    const float* src = dM + n * (int64_t)I::ROWS * C + chunk * 32;
+    float* dst = dMs + buf * TILE;
+    for (int i = threadIdx.x; i < I::ROWS * 8; i += WARPS * 32) cp_async16_b(dst + i * 4, src + (int64_t)(i >> 3) * C + (i & 7) * 4);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  stage(n0, 0);
+  for (int64_t n = n0; n < n1; ++n) {
+    const int buf = (int)(n - n0) & 1;
+    if (n + 1 < n1) {
+      stage(n + 1, buf ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();   // tile of node n (and, first time, the table) visible to all warps
+    const int eb = __ldg(row_ptr + n), ee = __ldg(row_ptr + n + 1);
+    const float* dMp = dMs + buf * TILE + lane;
+    for (int e = eb + wid; e < ee; e += WARPS) {
+      const int s = __ldg(sender + e);
+      const float yv = lane < ystride ? __ldg(Y + (int64_t)e * ystride + lane) : 0.f;
+      float x[DIN], dx[DIN];
+#pragma unroll
+      for (int d = 0; d < DIN; ++d) {
+        x[d] = __ldg(h + ((int64_t)s * DIN + d) * C + c);
+        dx[d] = 0.f;
+      }
+      __syncwarp();
+      for (int q = lane; q < I::NTAB; q += 32) {
+        const int4 t = tab_s[q];
+        const float y0 = __shfl_sync(0xffffffffu, yv, t.x);
+        const float y1 = __shfl_sync(0xffffffffu, yv, t.z);
+        Gs[q] = fmaf(__int_as_float(t.y), y0, __int_as_float(t.w) * y1);
+      }
+      __syncwarp();
+      float* dwp = dw + (int64_t)e * I::NPATHS * C + c;
+      I::run(x, reinterpret_cast<const float4*>(Gs), w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane, wstride, dMp, 32, C, dwp, dx);
+      if (inv_norm != 1.0f) {
+#pragma unroll
+        for (int p = 0; p < I::NPATHS; ++p) dwp[(int64_t)p * C] *= inv_norm;
+      }
+#pragma unroll
+      for (int d = 0; d < DIN; ++d) __stcs(dxe + ((int64_t)e * DIN + d) * C + c, dx[d] * inv_norm);
+    }
+    __syncthreads();   // every warp is done with tile `buf` before node n + 2 is staged into it
+  }
+}
+
 template <int LIN, int LMAX>
 int launch_tpb(const float* h, const float* Y, int ystride, const float* w_t, int64_t E, const int32_t* sender, const int32_t* row_ptr,
                float inv_norm, const float* dM, float* dw, float* dh, int64_t N, int C, cudaStream_t s) {
   using I = TpB<LIN, LMAX>;
-  const size_t smem = (size_t)I::NTAB * 16 + (size_t)WARPS * I::NTAB * 4;
+  // EEG_TPB_V=1: variant 1 (warp = 4 nodes, all loads global); default: variant 2 (CTA-shared node tile in shared memory)
+  static const int variant = getenv("EEG_TPB_V") ? atoi(getenv("EEG_TPB_V")) : 2;
+  const size_t smem1 = (size_t)I::NTAB * 16 + (size_t)WARPS * I::NTAB * 4;
+  const size_t smem = variant == 1 ? smem1 : smem1 + (size_t)2 * I::ROWS * 32 * 4;
   static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set && smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(k_tp_bwd<LIN, LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tp_bwd2<LIN, LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) {
       eeg_set_error("eeg_tp_scatter_bwd: cannot opt in to %zu B shared memory: %s", smem, cudaGetErrorString(e));
       return 2;
@@ -117,8 +201,12 @@ int launch_tpb(const float* h, const float* Y, int ystride, const float* w_t, in
     attr_set = true;
   }
   const int chunks = C / 32;
-  k_tp_bwd<LIN, LMAX><<<(unsigned)(eeg_div_up(N, WARPS * NPW) * chunks), WARPS * 32, smem, s>>>(h, Y, ystride, w_t, E, sender, row_ptr,
-                                                                                                inv_norm, dM, dw, dh, N, C, chunks);
+  if (variant == 1)
+    k_tp_bwd<LIN, LMAX><<<(unsigned)(eeg_div_up(N, WARPS * NPW) * chunks), WARPS * 32, smem, s>>>(h, Y, ystride, w_t, E, sender, row_ptr,
+                                                                                                  inv_norm, dM, dw, dh, N, C, chunks);
+  else
+    k_tp_bwd2<LIN, LMAX><<<(unsigned)(eeg_div_up(N, NPC2) * chunks), WARPS * 32, smem, s>>>(h, Y, ystride, w_t, E, sender, row_ptr, inv_norm,
+                                                                                           dM, dw, dh, N, C, chunks);
   EEG_CHECK_LAUNCH("eeg_tp_scatter_bwd");
   return 0;
 }
