@@ -122,10 +122,9 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict_
   constexpr int DIN = (LIN + 1) * (LIN + 1);
   constexpr int TILE = I::ROWS * 32;   // floats
   extern __shared__ __align__(16) uint8_t tpb_smem[];
-  int4* tab_s = reinterpret_cast<int4*>(tpb_smem);
-  float* Gall = reinterpret_cast<float*>(tpb_smem + (size_t)I::NTAB * 16);
+  const int4* __restrict__ tab_s = I::tab();   // read through L1 (coalesced int4): keeping it out of shared memory lets 3 CTAs share an SM
+  float* Gall = reinterpret_cast<float*>(tpb_smem);
   float* dMs = Gall + (size_t)WARPS * I::NTAB;   // [2][ROWS][32]
-  for (int i = threadIdx.x; i < I::NTAB; i += WARPS * 32) tab_s[i] = I::tab()[i];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   float* Gs = Gall + (size_t)wid * I::NTAB;
   const int chunk = blockIdx.x % chunks;
@@ -163,7 +162,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict_
       }
       __syncwarp();
       for (int q = lane; q < I::NTAB; q += 32) {
-        const int4 t = tab_s[q];
+        const int4 t = __ldg(tab_s + q);
         const float y0 = __shfl_sync(0xffffffffu, yv, t.x);
         const float y1 = __shfl_sync(0xffffffffu, yv, t.z);
         Gs[q] = fmaf(__int_as_float(t.y), y0, __int_as_float(t.w) * y1);
@@ -189,7 +188,7 @@ int launch_tpb(const float* h, const float* Y, int ystride, const float* w_t, in
   // EEG_TPB_V=1: variant 1 (warp = 4 nodes, all loads global); default: variant 2 (CTA-shared node tile in shared memory)
   static const int variant = getenv("EEG_TPB_V") ? atoi(getenv("EEG_TPB_V")) : 2;
   const size_t smem1 = (size_t)I::NTAB * 16 + (size_t)WARPS * I::NTAB * 4;
-  const size_t smem = variant == 1 ? smem1 : smem1 + (size_t)2 * I::ROWS * 32 * 4;
+  const size_t smem = variant == 1 ? smem1 : (size_t)WARPS * I::NTAB * 4 + (size_t)2 * I::ROWS * 32 * 4;
   static EegDevFlags attr_set_dev; bool& attr_set = eeg_dev_flag(attr_set_dev);
   if (!attr_set && smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(k_tp_bwd<LIN, LMAX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

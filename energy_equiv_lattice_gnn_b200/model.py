@@ -161,8 +161,10 @@ class EnergyEquivGNN(torch.nn.Module):
         if hit is not None and hit[0] == key:
             return hit[1]
         Wflat = torch.cat([w.detach() for w in ws], 0).contiguous()
+        prev_tag = nv.get_tag()
         nv.set_tag(f'L{i}.sc_coefficients')
         T = nv.sc_coefficients(self._a_row_ptr, self._a_col, self._a_val, self._wmap["n_coef"], Wflat, self.C)
+        nv.set_tag(prev_tag)   # callers evaluate this as an argument of the tagged sym_contract call
         self._cache[("sc", i)] = (key, T)
         return T
 
@@ -175,8 +177,10 @@ class EnergyEquivGNN(torch.nn.Module):
         hidden = lins[1:-1]
         Wh = torch.stack([l.weight.detach() for l in hidden]).contiguous() if hidden else None
         bh = torch.stack([l.bias.detach() for l in hidden]).contiguous() if hidden else lins[0].bias.detach().new_zeros(1, lins[0].weight.shape[0])
+        prev_tag = nv.get_tag()
         nv.set_tag(f'L{i}.radial_pack')
         img = nv.radial_pack(Wh, lins[-1].weight.detach().contiguous())
+        nv.set_tag(prev_tag)
         self._cache[("radial", i)] = (key, img, bh)
         return img, bh
 

@@ -82,6 +82,10 @@ def set_tag(tag: str):
     _tag = tag
 
 
+def get_tag() -> str:
+    return _tag
+
+
 def start_profile():
     global _events
     _events = []
@@ -578,7 +582,7 @@ def _guarded(fn):
 def _install_guards():
     import inspect
     g = globals()
-    skip = {"lib", "make_layout", "set_tag", "start_profile", "stop_profile"}
+    skip = {"lib", "make_layout", "set_tag", "get_tag", "start_profile", "stop_profile"}
     for name, fn in list(g.items()):
         if name.startswith("_") or name in skip or not inspect.isfunction(fn) or fn.__module__ != __name__:
             continue
