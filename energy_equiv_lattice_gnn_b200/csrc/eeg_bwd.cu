@@ -484,6 +484,53 @@ extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const flo
   return 0;
 }
 
+// ---- eeg_colsum_static: the deterministic column sum WITHOUT a caller workspace and without any allocation ----------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The CTA partials live in a file-scope
+// device array of EEG_COLSUM_STATIC_MAX_FLOATS floats (4 MiB), held by every GPU that loads the library until exit.
+// In HOST code `eeg_colsum_static_scratch` is only a stand-in for the symbol, not a device address: the launcher resolves it
+// once per device with cudaGetSymbolAddress (that device current) and passes the resolved pointer to the kernels.
+// Nothing in the scratch has to start at zero: every partial that k_colsum_reduce reads is written by k_colsum of the SAME
+// call first (all (row slice, column < cols) entries), so the contents left by an earlier call are never observed.
+// All calls on a device share the array: two calls that overlap on the GPU (different streams) race.
+#define EEG_COLSUM_STATIC_MAX_FLOATS (1 << 20)
+static __device__ __align__(256) float eeg_colsum_static_scratch[EEG_COLSUM_STATIC_MAX_FLOATS];
+
+extern "C" int64_t eeg_colsum_static_max_floats(void) { return EEG_COLSUM_STATIC_MAX_FLOATS; }
+
+extern "C" int eeg_colsum_static(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream) {
+  EEG_REQUIRE(R >= 0 && cols >= 0 && ld >= cols, "eeg_colsum_static: bad shape (R=%lld, ld=%d, cols=%d)", (long long)R, ld, cols);
+  if (R == 0 || cols == 0) return 0;
+  const int rows_per_cta = 256;
+  const int64_t parts = (R + rows_per_cta - 1) / rows_per_cta;
+  EEG_REQUIRE(parts * cols <= (int64_t)EEG_COLSUM_STATIC_MAX_FLOATS,
+              "eeg_colsum_static: ceil(R/256) * cols = %lld floats of scratch exceed the built-in maximum of %d; use eeg_colsum with a "
+              "caller workspace", (long long)(parts * cols), EEG_COLSUM_STATIC_MAX_FLOATS);
+  static float* scratch_of_device[64] = {};   // resolved device address of the array, per device ordinal
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    eeg_set_error("eeg_colsum_static: cudaGetDevice failed or device ordinal %d out of range: %s", dev, cudaGetErrorString(e));
+    return 2;
+  }
+  if (scratch_of_device[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, eeg_colsum_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      eeg_set_error("eeg_colsum_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return 2;
+    }
+    scratch_of_device[dev] = p;
+  }
+  float* ws = scratch_of_device[dev];
+  dim3 grid((unsigned)parts, (unsigned)((cols + 31) / 32));
+  k_colsum<<<grid, 256, 0, (cudaStream_t)stream>>>(x, R, ld, cols, row_scale, out, rows_per_cta, ws);
+  EEG_CHECK_LAUNCH("eeg_colsum_static");
+  k_colsum_reduce<<<(unsigned)((cols + 127) / 128), 128, 0, (cudaStream_t)stream>>>(ws, parts, cols, out);
+  EEG_CHECK_LAUNCH("eeg_colsum_static (reduce)");
+  return 0;
+}
+
 extern "C" int eeg_silu_fwd(const float* a, float* s, int64_t n, void* stream) {
   if (n == 0) return 0;
   k_silu_fwd<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(a, s, n);

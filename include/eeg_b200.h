@@ -141,6 +141,16 @@ int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, const EegLayout* 
  * ws: ceil(R / 256) * cols floats -> deterministic (CTA partials added in order); NULL -> atomicAdd. */
 int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,
                void* stream);
+/* Same result as eeg_colsum in its deterministic mode, with NO caller workspace and no allocation of any kind (no cudaMalloc /
+ * cudaFree / allocating library call).  This entry point has no counterpart in the reference: it was added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  The CTA partials go to a file-scope device array inside the library of eeg_colsum_static_max_floats()
+ * = 2^20 floats (4 MiB, held by every GPU that loads the library until exit); a call needing more than that, i.e.
+ * ceil(R / 256) * cols > 2^20, is rejected with return code 1 and a message - use eeg_colsum with a workspace then.
+ * out[c] += ... as for eeg_colsum (the caller zeroes out).  Every call on a device shares the one array: calls that overlap
+ * on the GPU (different streams) race; calls ordered on one stream are safe, and nothing has to be cleared between calls. */
+int eeg_colsum_static(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, void* stream);
+int64_t eeg_colsum_static_max_floats(void);
 /* out[n, :] = sum_{j in [ptr[n], ptr[n+1])} in[perm[j], :]  (rows of `width` floats, width % 4 == 0; fixed order): the
  * sender-side scatter of the tensor-product backward as a CSR walk instead of atomics. */
 int eeg_segment_sum_rows(const float* in, const int32_t* perm, const int32_t* ptr, int64_t N, int64_t width, float* out,
