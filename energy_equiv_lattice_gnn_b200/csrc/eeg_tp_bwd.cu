@@ -114,7 +114,7 @@ __device__ __forceinline__ void cp_async16_b(void* smem_dst, const void* gmem_sr
 }
 
 template <int LIN, int LMAX>
-__global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
+__global__ void __launch_bounds__(WARPS * 32, 3) k_tp_bwd2(const float* __restrict__ h, const float* __restrict__ Y, int ystride,
                                                         const float* __restrict__ w_t, int64_t E, const int32_t* __restrict__ sender,
                                                         const int32_t* __restrict__ row_ptr, float inv_norm, const float* __restrict__ dM,
                                                         float* __restrict__ dw, float* __restrict__ dxe, int64_t N, int C, int chunks) {
@@ -142,18 +142,23 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict_
   stage(n0, 0);
   for (int64_t n = n0; n < n1; ++n) {
     const int buf = (int)(n - n0) & 1;
-    if (n + 1 < n1) {
-      stage(n + 1, buf ^ 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    } else {
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-    }
-    __syncthreads();   // tile of node n (and, first time, the table) visible to all warps
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    // ONE barrier per node: tile n (staged during node n - 1) is visible to every warp, and every warp has finished reading
+    // tile n - 1, whose buffer the prefetch of tile n + 1 below overwrites.  (The first version used two barriers per node
+    // and sat 27 % of its stall samples there: profiles/r02_ncu_tp_bwd2_summary.txt.)
+    __syncthreads();
+    if (n + 1 < n1) stage(n + 1, buf ^ 1);
     const int eb = __ldg(row_ptr + n), ee = __ldg(row_ptr + n + 1);
     const float* dMp = dMs + buf * TILE + lane;
     for (int e = eb + wid; e < ee; e += WARPS) {
       const int s = __ldg(sender + e);
       const float yv = lane < ystride ? __ldg(Y + (int64_t)e * ystride + lane) : 0.f;
+      // all per-path weights of the edge first: 42 independent loads in flight while G is staged, instead of one exposed
+      // global-load latency per path inside the generated program (52 % long-scoreboard stalls)
+      float wreg[I::NPATHS];
+      const float* wsrc = w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane;
+#pragma unroll
+      for (int p = 0; p < I::NPATHS; ++p) wreg[p] = __ldg(wsrc + (int64_t)p * wstride);
       float x[DIN], dx[DIN];
 #pragma unroll
       for (int d = 0; d < DIN; ++d) {
@@ -169,7 +174,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict_
       }
       __syncwarp();
       float* dwp = dw + (int64_t)e * I::NPATHS * C + c;
-      I::run(x, reinterpret_cast<const float4*>(Gs), w_t + (int64_t)chunk * E * 32 + (int64_t)e * 32 + lane, wstride, dMp, 32, C, dwp, dx);
+      I::run(x, reinterpret_cast<const float4*>(Gs), wreg, 1, dMp, 32, C, dwp, dx);   // weights from registers (stride 1)
       if (inv_norm != 1.0f) {
 #pragma unroll
         for (int p = 0; p < I::NPATHS; ++p) dwp[(int64_t)p * C] *= inv_norm;
@@ -177,7 +182,6 @@ __global__ void __launch_bounds__(WARPS * 32) k_tp_bwd2(const float* __restrict_
 #pragma unroll
       for (int d = 0; d < DIN; ++d) __stcs(dxe + ((int64_t)e * DIN + d) * C + c, dx[d] * inv_norm);
     }
-    __syncthreads();   // every warp is done with tile `buf` before node n + 2 is staged into it
   }
 }
 
