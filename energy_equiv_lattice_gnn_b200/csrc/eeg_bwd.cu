@@ -29,12 +29,22 @@ struct WgParams {
 
 // Rows per CTA: enough row slices that the grid holds >= ~4 CTAs per SM (the K = 32 -> 32 linears have ONE 32 x 32 tile per
 // irrep block: with 4096 rows per CTA their weight gradients ran on 94 CTAs at 0.8 TB/s), multiple of 32, at most WG_ROWS_MAX.
+// K tile of a launch: 64 when every non-empty block has K >= 64, else 32 (the five 32 -> 32 mixes)
+static int wg_tile_k(const EegLayout* lin, const EegLayout* lout, const int32_t* k_override) {
+  int tk = 64;
+  for (int b = 0; b < lin->n_blocks; ++b) {
+    const int k = k_override ? k_override[b] : lin->mul[b], n = lout ? lout->mul[b] : 32;
+    if (k > 0 && n > 0 && k < 64) tk = 32;
+  }
+  return tk;
+}
 static int wg_rows_per_cta(const EegLayout* lin, const EegLayout* lout, const int32_t* k_override, int64_t N) {
+  const int TK = wg_tile_k(lin, lout, k_override);
   int64_t rows_tiles = 0;   // sum over blocks of rows * tiles
   for (int b = 0; b < lin->n_blocks; ++b) {
     const int k = k_override ? k_override[b] : lin->mul[b], n = lout ? lout->mul[b] : 32;
     if (k <= 0 || n <= 0) continue;
-    rows_tiles += N * lin->rows[b] * (int64_t)((k + 31) / 32) * ((n + 31) / 32);
+    rows_tiles += N * lin->rows[b] * (int64_t)((k + TK - 1) / TK) * ((n + 31) / 32);
   }
   int64_t r = rows_tiles / (4 * EEG_NUM_SMS);
   r = (r + 31) / 32 * 32;
@@ -46,10 +56,15 @@ static int wg_rows_per_cta(const EegLayout* lin, const EegLayout* lout, const in
 // ws != nullptr: deterministic mode - the row slice `cta / tiles` of a tile writes its partial sums to
 // ws[slice * ws_stride + element] (bias partials behind the weights at n_weights + column) and k_wgrad_reduce adds the
 // slices in order; ws == nullptr: one atomicAdd per element and slice (order depends on scheduling).
+// KPT = k values per thread: CTA tile = (16 * KPT) x 32 outputs, thread tile KPT x 4.  KPT = 4 (64 x 32 tile, used when every
+// block has K >= 64) needs two LDS.128 per 16 FMAs; the original KPT = 2 needed two loads per 8 FMAs and ran the K = 1344
+// radial-MLP and K = 160..320 interaction weight gradients at 17 TFLOP/s.  Rows are accumulated in the same order for both.
+template <int KPT>
 __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dW,
                                                       float* __restrict__ dbias, int64_t N, WgParams P, float* __restrict__ ws,
                                                       int64_t ws_stride, int64_t n_weights) {
-  __shared__ __align__(16) float Xs[32][36];
+  constexpr int TK = 16 * KPT, XLD = TK + 4;
+  __shared__ __align__(16) float Xs[32][XLD];
   __shared__ __align__(16) float Ys[32][36];
   int cta = blockIdx.x, bi = 0;
 #pragma unroll
@@ -61,9 +76,13 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
   const int kt = (cta % tiles) / d.ntiles, nt = (cta % tiles) % d.ntiles;
   const int64_t r_begin = (int64_t)(cta / tiles) * P.wg_rows, total = N * d.rows;
   const int64_t r_end = r_begin + P.wg_rows < total ? r_begin + P.wg_rows : total;
-  const int t = threadIdx.x, tk = t >> 3, tn = t & 7;   // thread: k = 2 tk + {0,1}, n = 4 tn + {0..3}
-  const int lr = t >> 2, lq = t & 3;                     // loader: row lr, float4 columns lq and lq + 4
-  float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+  const int t = threadIdx.x, tk = t >> 3, tn = t & 7;   // thread: k = KPT tk + {0..KPT-1}, n = 4 tn + {0..3}
+  const int lr = t >> 2, lq = t & 3;                     // loader: row lr, float4 columns lq, lq + 4, ...
+  float acc[KPT][4];
+#pragma unroll
+  for (int i = 0; i < KPT; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};
   const bool want_bias = dbias != nullptr && bi == 0 && kt == 0 && tk == 0;
   for (int64_t r0 = r_begin; r0 < r_end; r0 += 32) {
@@ -71,26 +90,39 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
     const bool ok = r < r_end;
     const int64_t n = ok ? r / d.rows : 0;
     const int m = ok ? (int)(r - n * d.rows) : 0;
-    const float* xr = x + n * P.in_stride + d.in_off + (int64_t)m * d.in_ld + kt * 32;
+    const float* xr = x + n * P.in_stride + d.in_off + (int64_t)m * d.in_ld + kt * TK;
     const float* yr = dy + n * P.out_stride + d.out_off + (int64_t)m * d.nout + nt * 32;
+#pragma unroll
+    for (int h = 0; h < TK / 16; ++h) {
+      const int c4 = (lq + 4 * h) * 4;
+      float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok && kt * TK + c4 < d.k) xv = __ldg(reinterpret_cast<const float4*>(xr + c4));
+      *reinterpret_cast<float4*>(&Xs[lr][c4]) = xv;
+    }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int c4 = (lq + 4 * h) * 4;
-      float4 xv = make_float4(0.f, 0.f, 0.f, 0.f), yv = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (ok && kt * 32 + c4 < d.k) xv = __ldg(reinterpret_cast<const float4*>(xr + c4));
+      float4 yv = make_float4(0.f, 0.f, 0.f, 0.f);
       if (ok && nt * 32 + c4 < d.nout) yv = __ldg(reinterpret_cast<const float4*>(yr + c4));
-      *reinterpret_cast<float4*>(&Xs[lr][c4]) = xv;
       *reinterpret_cast<float4*>(&Ys[lr][c4]) = yv;
     }
     __syncthreads();
 #pragma unroll 8
     for (int rr = 0; rr < 32; ++rr) {
-      const float2 a = *reinterpret_cast<const float2*>(&Xs[rr][2 * tk]);
+      float a[KPT];
+      if constexpr (KPT == 4) {
+        const float4 a4 = *reinterpret_cast<const float4*>(&Xs[rr][4 * tk]);
+        a[0] = a4.x; a[1] = a4.y; a[2] = a4.z; a[3] = a4.w;
+      } else {
+        const float2 a2 = *reinterpret_cast<const float2*>(&Xs[rr][2 * tk]);
+        a[0] = a2.x; a[1] = a2.y;
+      }
       const float4 b = *reinterpret_cast<const float4*>(&Ys[rr][4 * tn]);
-      acc[0][0] = fmaf(a.x, b.x, acc[0][0]); acc[0][1] = fmaf(a.x, b.y, acc[0][1]);
-      acc[0][2] = fmaf(a.x, b.z, acc[0][2]); acc[0][3] = fmaf(a.x, b.w, acc[0][3]);
-      acc[1][0] = fmaf(a.y, b.x, acc[1][0]); acc[1][1] = fmaf(a.y, b.y, acc[1][1]);
-      acc[1][2] = fmaf(a.y, b.z, acc[1][2]); acc[1][3] = fmaf(a.y, b.w, acc[1][3]);
+#pragma unroll
+      for (int i = 0; i < KPT; ++i) {
+        acc[i][0] = fmaf(a[i], b.x, acc[i][0]); acc[i][1] = fmaf(a[i], b.y, acc[i][1]);
+        acc[i][2] = fmaf(a[i], b.z, acc[i][2]); acc[i][3] = fmaf(a[i], b.w, acc[i][3]);
+      }
       if (want_bias) { bsum[0] += b.x; bsum[1] += b.y; bsum[2] += b.z; bsum[3] += b.w; }
     }
     __syncthreads();
@@ -98,10 +130,10 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
   float* const wsl = ws ? ws + (int64_t)(cta / tiles) * ws_stride : nullptr;
   float* Wb = (ws ? wsl : dW) + d.w_off;
 #pragma unroll
-  for (int i = 0; i < 2; ++i)
+  for (int i = 0; i < KPT; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int k = kt * 32 + 2 * tk + i, n = nt * 32 + 4 * tn + j;
+      const int k = kt * TK + KPT * tk + i, n = nt * 32 + 4 * tn + j;
       if (k < d.k && n < d.nout) {
         float* dst = Wb + (P.transB ? (int64_t)n * d.k + k : (int64_t)k * d.nout + n);
         if (ws) *dst = acc[i][j] * d.scale;
@@ -411,6 +443,7 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
   P.out_stride = lout->stride;
   P.transB = transB;
   P.wg_rows = wg_rows_per_cta(lin, lout, k_override, N);
+  const int TK = wg_tile_k(lin, lout, k_override);
   int64_t ctas = 0;
   for (int b = 0; b < P.n_blocks; ++b) {
     EEG_REQUIRE(lin->rows[b] == lout->rows[b], "eeg_block_linear_wgrad: block %d rows differ", b);
@@ -427,7 +460,7 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
                     lin->stride % 4 == 0 && lout->stride % 4 == 0,
                 "eeg_block_linear_wgrad: block %d not float4-aligned", b);
     d.cta_begin = (int)ctas;
-    d.ktiles = (d.k + 31) / 32;
+    d.ktiles = (d.k + TK - 1) / TK;
     d.ntiles = (d.nout + 31) / 32;
     const int64_t chunks = (N * d.rows + P.wg_rows - 1) / P.wg_rows;
     ctas += (d.k > 0 && d.nout > 0) ? chunks * d.ktiles * d.ntiles : 0;
@@ -448,7 +481,8 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
     EEG_REQUIRE(ws_floats >= slices * stride, "eeg_block_linear_wgrad: workspace too small (%lld < %lld floats)", (long long)ws_floats,
                 (long long)(slices * stride));
   }
-  k_linear_wgrad<<<(unsigned)ctas, 128, 0, (cudaStream_t)stream>>>(x, dy, dW, dbias, N, P, ws, stride, n_weights);
+  if (TK == 64) k_linear_wgrad<4><<<(unsigned)ctas, 128, 0, (cudaStream_t)stream>>>(x, dy, dW, dbias, N, P, ws, stride, n_weights);
+  else k_linear_wgrad<2><<<(unsigned)ctas, 128, 0, (cudaStream_t)stream>>>(x, dy, dW, dbias, N, P, ws, stride, n_weights);
   EEG_CHECK_LAUNCH("eeg_block_linear_wgrad");
   if (ws != nullptr) {
     k_wgrad_reduce<<<(unsigned)((stride + 255) / 256), 256, 0, (cudaStream_t)stream>>>(ws, stride, n_weights, bias_cols, dW, dbias, N, P);

@@ -8,7 +8,13 @@
 
 namespace {
 
-constexpr int CH = 2, TPC = 128, THREADS = CH * TPC, NT = 2 * TPC;   // 2 channels x 256 nodes per tile, node pairs per thread
+#ifndef EEG_SCB_TPC
+#define EEG_SCB_TPC 192
+#endif
+// 2 channels x (2 * TPC) nodes per tile, node pairs per thread.  TPC = 192 (12 warps per SM; 164 registers x 384 threads and
+// 214 KB of shared memory still fit one SM): the kernel is latency bound on its instruction stream (45 % no_inst stalls with 8
+// warps, profiles/r02_ncu_full_bwd_summary.txt), so more warps sharing the same stream pay off.
+constexpr int CH = 2, TPC = EEG_SCB_TPC, THREADS = CH * TPC, NT = 2 * TPC;
 
 typedef unsigned long long p2;  // two fp32 lanes (node A, node B)
 __device__ __forceinline__ p2 pk(float a, float b) { p2 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(a), "f"(b)); return d; }

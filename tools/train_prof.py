@@ -37,8 +37,10 @@ t_wall = time.perf_counter() - t0
 print(f"{G} lattices: device {e0.elapsed_time(e1) / K:.3f} ms/step, wall {t_wall / K * 1e3:.3f} ms/step, host enqueue {t_host / K * 1e3:.3f} ms/step")
 native.start_profile()
 tr.training_step(b)
-prof = {k: sum(v) for k, v in native.stop_profile().items()}
+raw = native.stop_profile()
+prof = {k: sum(v) for k, v in raw.items()}
 tot = sum(prof.values())
 print(f"sum of tagged device time: {tot:.3f} ms over {len(prof)} tags")
 for k, v in sorted(prof.items(), key=lambda kv: -kv[1]):
-    print(f"  {k:36s} {v:8.4f}")
+    calls = " ".join(f"{x:.3f}" for x in raw[k]) if len(raw[k]) > 1 else ""
+    print(f"  {k:36s} {v:8.4f}   {calls}")
