@@ -25,6 +25,9 @@ class _Forward(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dC):
+        if ctx.saved is None:
+            raise RuntimeError("EnergyEquivGNN: backward through the same forward a second time - the saved activations were freed "
+                               "after the first backward (run the forward again; retain_graph=True is not supported by the explicit backward)")
         grads = backward_impl(ctx.model, ctx.batch, ctx.saved, dC.contiguous().to(torch.float32))
         ctx.saved = None
         return (None, None, *grads)
@@ -129,7 +132,7 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         dB = nv.block_linear(dh, model._lay_h, Wp, offs, [sC] * nblk, model._lay_h, N, transB=True)
         # symmetric contraction
         x = sv["msg"][i]
-        T = model._sc_table(i)
+        T = sv["T"][i]   # the coefficient table the forward used
         nv.set_tag(f'bwd.L{i}.sym_contract_dx')
         dmsg = nv.sym_contract_bwd_x(lmax, model.correlation, C, x, dB, T, N)
         nv.set_tag(f'bwd.L{i}.sym_contract_dW')

@@ -267,3 +267,41 @@ extern "C" int eeg_edge_featurize(const float* pos, const int64_t* edge_index, c
   eeg_set_error("eeg_edge_featurize: unsupported (lmax=%d, nbasis=%d)", lmax, nbasis);
   return 1;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Input validation (opt-in): the CSR build and the edge featurisation index device memory with edge_index / batch as given
+// (torch_scatter and PyG would raise a device-side assert on a bad index; here a malformed batch - an index outside [0, N), a
+// graph id outside [0, G), a decreasing `batch` - would silently corrupt memory).  flags (one int32, zeroed here) collects
+//   bit 0: edge_index entry < 0 or >= N      bit 1: batch entry < 0 or >= G      bit 2: batch not non-decreasing
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void k_validate(const int64_t* __restrict__ edge_index, int64_t E, int64_t N, const int64_t* __restrict__ batch, int64_t G,
+                           int32_t* __restrict__ flags) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int f = 0;
+  if (i < 2 * E) {
+    const int64_t v = edge_index[i];
+    if (v < 0 || v >= N) f |= 1;
+  }
+  if (batch != nullptr && i < N) {
+    const int64_t b = batch[i];
+    if (b < 0 || b >= G) f |= 2;
+    if (i > 0 && batch[i - 1] > b) f |= 4;
+  }
+  if (f) atomicOr(flags, f);
+}
+
+extern "C" int eeg_graph_validate(const int64_t* edge_index, int64_t E, int64_t N, const int64_t* batch, int64_t G, int32_t* flags,
+                                  void* stream) {
+  EEG_REQUIRE(flags != nullptr && E >= 0 && N >= 0, "eeg_graph_validate: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int32_t), s);
+  if (e != cudaSuccess) {
+    eeg_set_error("eeg_graph_validate: memset failed: %s", cudaGetErrorString(e));
+    return 2;
+  }
+  const int64_t n = 2 * E > N ? 2 * E : N;
+  if (n == 0) return 0;
+  k_validate<<<eeg_div_up(n, 256), 256, 0, s>>>(edge_index, E, N, batch, G, flags);
+  EEG_CHECK_LAUNCH("eeg_graph_validate");
+  return 0;
+}

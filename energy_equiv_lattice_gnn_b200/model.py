@@ -150,6 +150,9 @@ class EnergyEquivGNN(torch.nn.Module):
         self._lay_g = nv.make_layout(rows_l, [C] * (lmax + 1))
         self._lay_o = nv.make_layout(rows_l, self.rmul)
         self._cache: Dict = {}
+        # True: check edge_index / batch ranges and the ordering of `batch` on every forward (one small kernel + a host
+        # synchronisation; the kernels index device memory with these tensors unchecked).  EEG_VALIDATE=1 turns it on globally.
+        self.validate_inputs = os.environ.get("EEG_VALIDATE", "0") not in ("", "0")
 
     # ------------------------------------------------------------------------------------------------------------------
     def _sc_table(self, i: int) -> torch.Tensor:
@@ -231,6 +234,9 @@ class EnergyEquivGNN(torch.nn.Module):
         edge_index = batch.edge_index.contiguous()
         N, G = batch.node_attrs.shape[0], int(batch.num_graphs)
         f32 = torch.float32
+        if self.validate_inputs:
+            nv.set_tag('validate')
+            nv.graph_validate(edge_index, N, batch.batch.contiguous(), G)
         nv.set_tag('csr')
         row_ptr, perm = nv.csr_build(edge_index, N)
         nv.set_tag('graph_ptr')
@@ -245,7 +251,7 @@ class EnergyEquivGNN(torch.nn.Module):
         h = nv.node_embed(batch.node_attrs.to(f32).contiguous(), emb.weight.detach().reshape(-1).contiguous(), emb.bias.detach())
         sC = 1.0 / math.sqrt(C)
         if save is not None:
-            save.update(row_ptr=row_ptr, perm=perm, gp=gp, Y=Y, f=f, snd=snd, h_in=[], hup=[], acts=[], w=[], M=[], msg=[], B=[])
+            save.update(row_ptr=row_ptr, perm=perm, gp=gp, Y=Y, f=f, snd=snd, h_in=[], hup=[], acts=[], w=[], M=[], msg=[], B=[], T=[])
         o_chain = hup_next = None
         for i, layer in enumerate(head.layers):
             inter, prod = layer.interaction, layer.product
@@ -282,7 +288,10 @@ class EnergyEquivGNN(torch.nn.Module):
             msg = nv.block_linear(M, self._lay_M[i], inter.linear.weight.detach(), woff, [1.0 / math.sqrt(n * C) for n in n_l],
                                   self._lay_h, N, bias=inter.linear.bias.detach())
             nv.set_tag(f'L{i}.sym_contract')
-            B = nv.sym_contract(lmax, self.correlation, C, msg, self._sc_table(i), N)
+            T = self._sc_table(i)
+            if save is not None:
+                save["T"].append(T)   # the backward differentiates THIS table, even if the weights change before it runs
+            B = nv.sym_contract(lmax, self.correlation, C, msg, T, N)
             poff = [b * C * C for b in range(lmax + 1)]
             if save is None and i == len(head.layers) - 1 and os.environ.get("EEG_READOUT_CHAIN", "1") != "0":
                 # inference, last layer: product.linear (+ residual) -> linear_1 -> Gate -> linear_2 chained in one pass;

@@ -24,7 +24,7 @@ SYMBOLS = [
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
     "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
     "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd", "eeg_segment_sum_rows",
-    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd", "eeg_blocks32_transpose",
+    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd", "eeg_blocks32_transpose", "eeg_graph_validate",
 ]
 
 
@@ -150,6 +150,19 @@ def csr_build(edge_index: torch.Tensor, n_nodes: int):
     _check(lib().eeg_csr_build(_p(edge_index, i64), C.c_int64(E), C.c_int64(n_nodes), _p(row_ptr), _p(perm), _p(ws),
                                C.c_size_t(nbytes), _stream()), "eeg_csr_build")
     return row_ptr, perm
+
+
+def graph_validate(edge_index: torch.Tensor, n_nodes: int, batch: Optional[torch.Tensor], num_graphs: int) -> None:
+    """Raise ValueError on an out-of-range edge_index / batch entry or a decreasing `batch` (one small kernel + a host read)."""
+    flags = torch.empty(1, dtype=i32, device=edge_index.device)
+    _begin("eeg_graph_validate")
+    _check(lib().eeg_graph_validate(_p(edge_index, i64), C.c_int64(edge_index.shape[1]), C.c_int64(n_nodes), _p(batch, i64) if batch is not None
+                                    else C.c_void_p(0), C.c_int64(num_graphs), _p(flags), _stream()), "eeg_graph_validate")
+    f = int(flags.item())
+    if f:
+        what = [m for bit, m in ((1, f"edge_index has entries outside [0, {n_nodes})"), (2, f"batch has entries outside [0, {num_graphs})"),
+                                 (4, "batch is not non-decreasing")) if f & bit]
+        raise ValueError("malformed graph batch: " + "; ".join(what))
 
 
 def graph_ptr(batch: torch.Tensor, num_graphs: int):

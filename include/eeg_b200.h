@@ -41,6 +41,14 @@ int eeg_csr_build(const int64_t* edge_index, int64_t E, int64_t N, int32_t* row_
 /* batch int64 [N] non-decreasing graph id (PyG Batch.batch; gnn/model.py:100-106) -> graph_ptr int32 [G+1] */
 int eeg_graph_ptr(const int64_t* batch, int64_t N, int64_t G, int32_t* graph_ptr, void* stream);
 
+/* Optional validation of the graph inputs the kernels index with (torch_scatter / PyG would assert on the device; these kernels
+ * do not check).  Writes one int32 to `flags` (device): bit 0 = an edge_index entry outside [0, N), bit 1 = a batch entry outside
+ * [0, G), bit 2 = batch is not non-decreasing (required by eeg_graph_ptr; gnn/model.py:100-106 relies on it through
+ * scatter(mean)).  batch may be NULL.  PRECONDITION of eeg_csr_build / eeg_edge_featurize / eeg_graph_ptr when this is skipped:
+ * all three conditions hold. */
+int eeg_graph_validate(const int64_t* edge_index, int64_t E, int64_t N, const int64_t* batch, int64_t G, int32_t* flags,
+                       void* stream);
+
 /* ---- node embedding: torch.nn.Linear(1, C) on node_attrs [N,1] (gnn/model.py:122,142): out[n,c] = a[n]*W[c] + b[c] */
 int eeg_node_embed_fwd(const float* node_attrs, const float* W /*[C,1]*/, const float* b /*[C]*/, float* out /*[N,C]*/,
                        int64_t N, int C, void* stream);

@@ -172,3 +172,30 @@ def test_streaming_predictor_matches_direct_calls(cuda_device):
     for g, w in zip(got, want):
         assert g.shape == w.shape and torch.equal(g, w)
     assert list(StreamingPredictor(model).run([])) == []
+
+
+def test_validate_inputs_rejects_malformed_batches(cuda_device):
+    """Opt-in input validation: an edge index >= N, a graph id >= G or a decreasing `batch` raise instead of
+    corrupting device memory; a well-formed batch passes and gives the same result as without validation."""
+    batch, rmax = synthetic_batch(range(1200, 1203))
+    oracle, params = make_pair(rmax)
+    model = cuda_model_from(oracle, params, cuda_device)
+    good = batch.to(cuda_device)
+    with torch.no_grad():
+        want = model(good)["stiffness"]
+        model.validate_inputs = True
+        assert torch.equal(model(good)["stiffness"], want)
+        bad = good.to(cuda_device)
+        bad.edge_index = good.edge_index.clone()
+        bad.edge_index[1, 5] = good.positions.shape[0]          # receiver == N
+        with pytest.raises(ValueError, match="edge_index"):
+            model(bad)
+        bad = good.to(cuda_device)
+        bad.batch = good.batch.clone()
+        bad.batch[3] = 2                                          # node of graph 0 labelled 2: not non-decreasing
+        with pytest.raises(ValueError, match="non-decreasing"):
+            model(bad)
+        bad.batch = good.batch.clone()
+        bad.batch[-1] = 3                                         # graph id == G
+        with pytest.raises(ValueError, match="batch has entries"):
+            model(bad)
