@@ -7,6 +7,8 @@
 //                            (gnn/model.py:100-111, gnn/blocks.py:185-229,392-442) + eeg_tail_wgrad for its weights
 // The input-gradient of a linear is eeg_block_linear_fwd with transB = 1 (dX = dY W^T).
 #include <math.h>
+#include <stdlib.h>
+#include <string.h>
 #include "eeg_common.cuh"
 #include "eeg_eig6.cuh"
 
@@ -431,12 +433,44 @@ void fill_tail(TailBwdParams& T, const EegLayout* lo, const int32_t* host_qmul, 
 
 }  // namespace
 
+// tensor-core path for the wide weight matrices (eeg_wgrad_umma.cu)
+int64_t eeg_wgrad_umma_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t N);
+int eeg_wgrad_umma_launch(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout, const int64_t* host_w_off,
+                          const float* host_scale, int transB, float* dW, int64_t N, float* ws, int64_t ws_floats, cudaStream_t stream);
+extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,
+                          void* stream);
+static bool wg_use_tc() {
+  static const char* env = getenv("EEG_WGRAD");   // "cuda": keep every weight gradient on the CUDA-core kernel (A/B timing)
+  return !(env && !strcmp(env, "cuda"));
+}
+// workspace of the tensor-core path incl. the bias partials behind it; -1 when the call cannot take that path
+static int64_t wg_umma_need(const EegLayout* lin, const EegLayout* lout, int bias_cols, int64_t N, int64_t* bias_need) {
+  *bias_need = 0;
+  if (!wg_use_tc()) return -1;
+  const int64_t un = eeg_wgrad_umma_ws_floats(lin, lout, N);
+  if (un < 0) return -1;
+  if (bias_cols > 0) {
+    if (lin->rows[0] != 1 || lout->mul[0] != bias_cols) return -1;
+    *bias_need = (N + 255) / 256 * bias_cols;
+  }
+  return un;
+}
+
 extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
                                       const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
                                       const int32_t* k_override, float* dW, float* dbias, int64_t N, int64_t n_weights, float* ws,
                                       int64_t ws_floats, void* stream) {
   EEG_REQUIRE(lin && lout && lin->n_blocks == lout->n_blocks && lin->n_blocks <= EEG_MAX_L, "eeg_block_linear_wgrad: layout mismatch");
   if (N == 0) return 0;
+  if (ws != nullptr && in_ld == nullptr && k_override == nullptr) {
+    int64_t bias_need = 0;
+    const int64_t un = wg_umma_need(lin, lout, dbias ? lout->mul[0] : 0, N, &bias_need);
+    if (un >= 0 && ws_floats >= un + bias_need) {
+      const int rc = eeg_wgrad_umma_launch(x, lin, dy, lout, host_w_off, host_scale, transB, dW, N, ws, un, (cudaStream_t)stream);
+      if (rc > 0) return rc;
+      if (rc == 0) return dbias ? eeg_colsum(dy + lout->off[0], N, lout->stride, lout->mul[0], nullptr, dbias, ws + un, bias_need, stream) : 0;
+    }
+  }
   WgParams P;
   P.n_blocks = lin->n_blocks;
   P.in_stride = lin->stride;
@@ -500,7 +534,10 @@ extern "C" int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, const 
     const int64_t sl = (N * lin->rows[b] + wg_rows - 1) / wg_rows;
     if (sl > slices) slices = sl;
   }
-  return slices * (n_weights + bias_cols);
+  int64_t need = slices * (n_weights + bias_cols), bias_need = 0;
+  const int64_t un = lin && lout ? wg_umma_need(lin, lout, bias_cols, N, &bias_need) : -1;
+  if (un >= 0 && un + bias_need > need) need = un + bias_need;
+  return need;
 }
 
 extern "C" int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,

@@ -114,3 +114,30 @@ def test_stages_match_reference_intermediates(cuda_device, name):
     if lmax < 4:
         q_ref = q_ref[:, :12]
     assert rel(save["q"][:, :q_ref.shape[1]], q_ref) < tol
+
+
+@pytest.mark.parametrize("rows,k_in,R", [([1], [1344], 20003), ([1], [192], 30001), ([1, 3], [128, 320], 4099)])
+def test_wide_weight_gradient_on_tensor_cores(cuda_device, rows, k_in, R):
+    """eeg_block_linear_wgrad for 64 output columns and >= 128 weight rows runs on tcgen05 (csrc/eeg_wgrad_umma.cu; the last
+    radial-MLP layer's dW = dw^T act, gnn/blocks.py:538-549): against torch fp64 at 1e-5 of the max, bitwise repeatable, with
+    a row count that is not a multiple of the stage (8) or pass length, ragged last weight tile (1344 = 10.5 x 128, 192, 320),
+    several rows per node, a bias gradient, and accumulation into a non-zero dW."""
+    g = torch.Generator().manual_seed(7 + R)
+    lin, lout = nv.make_layout(rows, k_in), nv.make_layout(rows, [64] * len(rows))
+    x = torch.randn(R, lin.stride, generator=g).to(cuda_device)
+    dy = torch.randn(R, lout.stride, generator=g).to(cuda_device)
+    w_off, n_w = [], 0
+    for k in k_in:
+        w_off.append(n_w)
+        n_w += k * 64
+    scale = [0.5 + 0.25 * b for b in range(len(rows))]
+    assert nv.lib().eeg_block_linear_wgrad_ws_floats is not None
+    got, gb = nv.linear_wgrad(x, lin, dy, lout, w_off, scale, n_w, R, want_bias=64)
+    again, gb2 = nv.linear_wgrad(x, lin, dy, lout, w_off, scale, n_w, R, want_bias=64)
+    assert torch.equal(got, again) and torch.equal(gb, gb2)
+    for b, (r, k) in enumerate(zip(rows, k_in)):
+        xb = x[:, lin.off[b]:lin.off[b] + r * k].reshape(R * r, k).double()
+        yb = dy[:, lout.off[b]:lout.off[b] + r * 64].reshape(R * r, 64).double()
+        ref = scale[b] * xb.t() @ yb
+        assert rel(got[w_off[b]:w_off[b] + k * 64].view(k, 64), ref) < 1e-5
+    assert rel(gb, dy[:, :64].double().sum(0)) < 1e-5
