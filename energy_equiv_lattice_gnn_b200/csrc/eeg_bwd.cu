@@ -87,7 +87,10 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};
   const bool want_bias = dbias != nullptr && bi == 0 && kt == 0 && tk == 0;
-  for (int64_t r0 = r_begin; r0 < r_end; r0 += 32) {
+  // the next 32-row chunk is loaded into registers while the current one is multiplied (the loop was bound by the exposed
+  // load latency: two barriers and one global round trip per 32 rows)
+  float4 xv[TK / 16], yv[2];
+  auto fetch = [&](int64_t r0) {
     const int64_t r = r0 + lr;
     const bool ok = r < r_end;
     const int64_t n = ok ? r / d.rows : 0;
@@ -97,18 +100,22 @@ __global__ void __launch_bounds__(128) k_linear_wgrad(const float* __restrict__ 
 #pragma unroll
     for (int h = 0; h < TK / 16; ++h) {
       const int c4 = (lq + 4 * h) * 4;
-      float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (ok && kt * TK + c4 < d.k) xv = __ldg(reinterpret_cast<const float4*>(xr + c4));
-      *reinterpret_cast<float4*>(&Xs[lr][c4]) = xv;
+      xv[h] = (ok && kt * TK + c4 < d.k) ? __ldg(reinterpret_cast<const float4*>(xr + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const int c4 = (lq + 4 * h) * 4;
-      float4 yv = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (ok && nt * 32 + c4 < d.nout) yv = __ldg(reinterpret_cast<const float4*>(yr + c4));
-      *reinterpret_cast<float4*>(&Ys[lr][c4]) = yv;
+      yv[h] = (ok && nt * 32 + c4 < d.nout) ? __ldg(reinterpret_cast<const float4*>(yr + c4)) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+  };
+  if (r_begin < r_end) fetch(r_begin);
+  for (int64_t r0 = r_begin; r0 < r_end; r0 += 32) {
+#pragma unroll
+    for (int h = 0; h < TK / 16; ++h) *reinterpret_cast<float4*>(&Xs[lr][(lq + 4 * h) * 4]) = xv[h];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) *reinterpret_cast<float4*>(&Ys[lr][(lq + 4 * h) * 4]) = yv[h];
     __syncthreads();
+    if (r0 + 32 < r_end) fetch(r0 + 32);
 #pragma unroll 8
     for (int rr = 0; rr < 32; ++rr) {
       float a[KPT];

@@ -28,6 +28,9 @@ struct LinearParams {
   int transB, act;
 };
 
+// PREFETCH: the next K-step is loaded into registers during the current one's FMAs (K = 1344: 0.376 -> 0.349 ms); with only two
+// K-steps (K = 32 -> 160..320) the extra registers cost more than the overlap gains (0.348 -> 0.368 ms), so K < 64 loads in place.
+template <bool PREFETCH>
 __global__ void __launch_bounds__(256) k_block_linear(const float* __restrict__ in, const float* __restrict__ W,
                                                       const float* __restrict__ bias, const float* __restrict__ residual,
                                                       float* __restrict__ out, int64_t N, LinearParams P) {
@@ -67,40 +70,47 @@ __global__ void __launch_bounds__(256) k_block_linear(const float* __restrict__ 
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
-  for (int k0 = 0; k0 < d.k; k0 += BK) {
-    // ---- A tile (transposed into smem)
+  // the next K-step's A / B pieces are loaded into registers while the current one is multiplied
+  float4 av4[2], bv4;
+  auto fetch = [&](int k0) {
 #pragma unroll
-    for (int it = 0; it < 2; ++it) {
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (a_ok[it] && k0 + a_kq * 4 < d.k) v = __ldg(reinterpret_cast<const float4*>(a_ptr[it] + k0));
-      int r = a_r + 64 * it;
-      As[a_kq * 4 + 0][r] = v.x;
-      As[a_kq * 4 + 1][r] = v.y;
-      As[a_kq * 4 + 2][r] = v.z;
-      As[a_kq * 4 + 3][r] = v.w;
-    }
-    // ---- B tile
-    if (!P.transB) {
-      // W[k][n]: 16 rows x 32 cols = 128 float4; threads 0..127
-      if (t < 128) {
-        int kk = t >> 3, c4 = (t & 7) * 4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (k0 + kk < d.k && n0 + c4 < d.nout) v = __ldg(reinterpret_cast<const float4*>(Wb + (int64_t)(k0 + kk) * d.nout + n0 + c4));
-        *reinterpret_cast<float4*>(&Bs[kk][c4]) = v;
+    for (int it = 0; it < 2; ++it)
+      av4[it] = (a_ok[it] && k0 + a_kq * 4 < d.k) ? __ldg(reinterpret_cast<const float4*>(a_ptr[it] + k0)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    bv4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t < 128) {
+      if (!P.transB) {   // W[k][n]: 16 rows x 32 cols = 128 float4
+        const int kk = t >> 3, c4 = (t & 7) * 4;
+        if (k0 + kk < d.k && n0 + c4 < d.nout) bv4 = __ldg(reinterpret_cast<const float4*>(Wb + (int64_t)(k0 + kk) * d.nout + n0 + c4));
+      } else {           // W[n][k]: 32 cols x 16 k = 128 float4 along k
+        const int c = t >> 2, kq = t & 3;
+        if (n0 + c < d.nout && k0 + kq * 4 < d.k) bv4 = __ldg(reinterpret_cast<const float4*>(Wb + (int64_t)(n0 + c) * d.k + k0 + kq * 4));
       }
-    } else {
-      // W[n][k]: 32 cols x 16 k = 128 float4 along k
-      if (t < 128) {
-        int c = t >> 2, kq = t & 3;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (n0 + c < d.nout && k0 + kq * 4 < d.k) v = __ldg(reinterpret_cast<const float4*>(Wb + (int64_t)(n0 + c) * d.k + k0 + kq * 4));
-        Bs[kq * 4 + 0][c] = v.x;
-        Bs[kq * 4 + 1][c] = v.y;
-        Bs[kq * 4 + 2][c] = v.z;
-        Bs[kq * 4 + 3][c] = v.w;
+    }
+  };
+  if (PREFETCH) fetch(0);
+  for (int k0 = 0; k0 < d.k; k0 += BK) {
+    if (!PREFETCH) fetch(k0);
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {   // A tile, transposed into smem
+      const int r = a_r + 64 * it;
+      As[a_kq * 4 + 0][r] = av4[it].x;
+      As[a_kq * 4 + 1][r] = av4[it].y;
+      As[a_kq * 4 + 2][r] = av4[it].z;
+      As[a_kq * 4 + 3][r] = av4[it].w;
+    }
+    if (t < 128) {
+      if (!P.transB) {
+        *reinterpret_cast<float4*>(&Bs[t >> 3][(t & 7) * 4]) = bv4;
+      } else {
+        const int c = t >> 2, kq = t & 3;
+        Bs[kq * 4 + 0][c] = bv4.x;
+        Bs[kq * 4 + 1][c] = bv4.y;
+        Bs[kq * 4 + 2][c] = bv4.z;
+        Bs[kq * 4 + 3][c] = bv4.w;
       }
     }
     __syncthreads();
+    if (PREFETCH && k0 + BK < d.k) fetch(k0 + BK);
 #pragma unroll
     for (int kk = 0; kk < BK; ++kk) {
       const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
@@ -256,7 +266,11 @@ extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const
     EEG_REQUIRE(tiles < (1LL << 31), "eeg_block_linear_fwd: too many tiles");
   }
   if (tiles == 0) return 0;
-  k_block_linear<<<(unsigned)tiles, 256, 0, (cudaStream_t)stream>>>(in, W, bias, residual, out, N, P);
+  int max_k = 0;
+  for (int b = 0; b < P.n_blocks; ++b)
+    if (P.b[b].nout > 0 && P.b[b].k > max_k) max_k = P.b[b].k;
+  if (max_k >= 64) k_block_linear<true><<<(unsigned)tiles, 256, 0, (cudaStream_t)stream>>>(in, W, bias, residual, out, N, P);
+  else k_block_linear<false><<<(unsigned)tiles, 256, 0, (cudaStream_t)stream>>>(in, W, bias, residual, out, N, P);
   EEG_CHECK_LAUNCH("eeg_block_linear_fwd");
   return 0;
 }
