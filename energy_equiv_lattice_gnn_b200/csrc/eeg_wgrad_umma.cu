@@ -24,7 +24,9 @@
 // Measured alternatives (radial-MLP shape, 512 lattices; the CUDA-core kernel takes 0.475 ms):
 //   per-thread LDG.32 straight into registers: 2.6 warp instructions per element of address arithmetic, 0.23 ms;
 //   one cp.async.bulk per row (2 KB / 256 B) from a loader warp: ~110 clk per bulk copy whatever its size, 0.19-0.22 ms.
+#include <cuda.h>   // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint, libcuda is not linked)
 #include <stdlib.h>
+#include <string.h>
 #include "eeg_common.cuh"
 #include "eeg_umma.cuh"
 
@@ -38,8 +40,9 @@ constexpr int WU_PASS_ROWS = 512;                 // most rows accumulated in TM
 constexpr int WU_MAXT = 4;                        // 128-row weight tiles per work item
 constexpr int WU_MAXN = 64;                       // output columns (nout = 32 or 64)
 constexpr int WU_XFORM = 512;                     // transform threads (16 warps)
-constexpr int WU_MMA_WARP = WU_XFORM / 32;
-constexpr int WU_THREADS = WU_XFORM + 32;
+constexpr int WU_MMA_WARP = WU_XFORM / 32, WU_TMA_WARP = WU_MMA_WARP + 1;
+constexpr int WU_THREADS = WU_XFORM + 64;
+constexpr int WU_BOXC = 256;                      // columns of one TMA box of x (the hardware limit per box dimension)
 constexpr int WU_MAXG = 16;                       // (block, tile group) pairs per launch
 constexpr uint32_t WU_LBO = 128 * 16;             // bytes between 4-row K-chunks of an A tile
 constexpr uint32_t WU_TERM = WU_CH * WU_LBO;      // 4096 B: one term (hi or lo) of one tile
@@ -52,7 +55,7 @@ constexpr int WU_CPT = WU_ROWS * WU_MAXT * 128 / 4 / 512;   // 16-byte copy chun
 constexpr int WU_XLD = WU_MAXT * 128;             // floats per raw x row
 constexpr uint32_t WU_RAWX = WU_ROWS * WU_XLD * 4;     // 16384 B
 constexpr uint32_t WU_RAW = WU_RAWX + WU_ROWS * WU_MAXN * 4;   // 18432 B: one raw stage (x rows, then dy rows)
-constexpr uint32_t WU_BAR_OFF = WU_OS * WU_OP + WU_RS * WU_RAW;
+constexpr uint32_t WU_BAR_OFF = WU_OS * WU_OP + WU_RS * WU_RAW;   // multiple of 1024: raw stages stay 128-byte aligned for TMA
 constexpr uint32_t WU_SMEM = WU_BAR_OFF + 256;
 
 struct WuGroup {
@@ -91,15 +94,30 @@ __device__ __forceinline__ float wu_hi(float x) { return __uint_as_float((__floa
 // [5] issuing, [6] waiting for the drain; [7] whole kernel.
 __device__ unsigned long long wu_prof[8];
 
+// 2-D tiled TMA load (cp.async.bulk.tensor): box (c0.., r0..) of the tensor map -> dense [box rows][box cols] in shared memory
+__device__ __forceinline__ void wu_tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int r0, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// TMA = true (one irrep block with one row per node: x and dy are plain 2-D row-major matrices, the radial-MLP case): a loader
+// warp issues three tensor-map loads per stage (two [8 x 256] boxes of x, one [8 x nout] box of dy; rows and columns past the
+// ends are zero-filled by the hardware) into the raw ring.  TMA = false: the transform warps issue per-thread cp.async instead.
+template <bool TMA>
 __global__ void __launch_bounds__(WU_THREADS, 1)
-k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ ws, const WuParams P) {
+k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ ws, const WuParams P,
+             const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_y) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* const raw = smem + WU_OS * WU_OP;
   uint64_t* op_full = reinterpret_cast<uint64_t*>(smem + WU_BAR_OFF);    // [OS] transform warps (16 arrivals) -> MMA
   uint64_t* op_empty = op_full + WU_OS;                                  // [OS] MMA commit -> transform warps
   uint64_t* acc_full = op_empty + WU_OS;                                 // MMA commit at the end of a pass -> drain
   uint64_t* acc_empty = acc_full + 1;                                    // drained (16 arrivals) -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 1);
+  uint64_t* raw_full = acc_empty + 1;                                    // [RS] TMA bytes -> transform warps      (TMA only)
+  uint64_t* raw_empty = raw_full + WU_RS;                                // [RS] transform warps (16) -> loader    (TMA only)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(raw_empty + WU_RS);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool prof = P.prof && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == WU_MMA_WARP);
   long long pc[4] = {0, 0, 0, 0}, t_start = prof ? clock64() : 0, t0 = t_start;
@@ -126,6 +144,7 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
     for (int s = 0; s < WU_OS; ++s) { mbar_init(&op_full[s], WU_XFORM / 32); mbar_init(&op_empty[s], 1); }
     mbar_init(acc_full, 1);
     mbar_init(acc_empty, WU_XFORM / 32);
+    for (int s = 0; s < WU_RS; ++s) { mbar_init(&raw_full[s], 1); mbar_init(&raw_empty[s], WU_XFORM / 32); }
     mbar_fence_init();
   }
   if (warp == WU_MMA_WARP) tmem_alloc(tmem_slot, 512);
@@ -185,8 +204,10 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
     }
     const int quarter = warp & 3, sub = warp >> 2, pieces = d.nout / 16;
     const uint32_t lane_base = ((uint32_t)(quarter * 32)) << 16;
+    if (!TMA) {
 #pragma unroll 1
-    for (int st = 0; st < WU_RS - 1; ++st) issue(st);
+      for (int st = 0; st < WU_RS - 1; ++st) issue(st);
+    }
     tick(2);
     for (int st = 0; st < n_stages; ++st) {
       const int os = st % WU_OS;
@@ -194,11 +215,16 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
       const float* ry = rx + WU_ROWS * WU_XLD;
       uint8_t* a_st = smem + (size_t)os * WU_OP;
       uint8_t* b_st = a_st + WU_A_BYTES;
-      wu_cp_wait<WU_RS - 2>();   // this thread's chunks of stage st have landed
-      wu_bar_xform();            // ... everyone's have, and everyone has finished reading stage st - 1
-      tick(0);
-      issue(st + WU_RS - 1);     // refill the slot of stage st - 1
-      tick(2);
+      if (TMA) {
+        wu_wait<20>(&raw_full[st % WU_RS], (st / WU_RS) & 1);
+        tick(0);
+      } else {
+        wu_cp_wait<WU_RS - 2>();   // this thread's chunks of stage st have landed
+        wu_bar_xform();            // ... everyone's have, and everyone has finished reading stage st - 1
+        tick(0);
+        issue(st + WU_RS - 1);     // refill the slot of stage st - 1
+        tick(2);
+      }
       wu_wait<20>(&op_empty[os], ((st / WU_OS) & 1) ^ 1);
       tick(1);
 #pragma unroll
@@ -207,7 +233,8 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
           const int q = aq[i], c = ac[i];
           float v[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) v[j] = rx[(4 * q + j) * WU_XLD + c];
+          for (int j = 0; j < 4; ++j)   // TMA: [box][row][256 columns]; cp.async: [row][512 columns]
+            v[j] = TMA ? rx[(c >> 8) * (WU_ROWS * WU_BOXC) + (4 * q + j) * WU_BOXC + (c & (WU_BOXC - 1))] : rx[(4 * q + j) * WU_XLD + c];
           float4 hi, lo;
           hi.x = wu_hi(v[0]); hi.y = wu_hi(v[1]); hi.z = wu_hi(v[2]); hi.w = wu_hi(v[3]);
           lo.x = v[0] - hi.x; lo.y = v[1] - hi.y; lo.z = v[2] - hi.z; lo.w = v[3] - hi.w;
@@ -229,7 +256,10 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
       }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&op_full[os]);
+      if (lane == 0) {
+        mbar_arrive(&op_full[os]);
+        if (TMA) mbar_arrive(&raw_empty[st % WU_RS]);   // this warp's raw values are in registers / operand tiles
+      }
       tick(2);
       if ((st + 1) % d.spp == 0 || st + 1 == n_stages) {
         // ---- end of a pass: drain.  TMEM lane = weight row inside the tile; warp w reads lanes 32 (w % 4) ..., the 4 warps of a
@@ -257,8 +287,8 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
     wu_cp_wait<0>();
     if (prof)
       for (int k = 0; k < 4; ++k) atomicAdd(&wu_prof[k], (unsigned long long)pc[k]);
-  } else if (warp == WU_MMA_WARP) {
-    if (lane == 0) {
+  } else if (warp == WU_MMA_WARP && lane == 0) {
+    {
       // ============================================================ MMA issuer
       const uint32_t idesc_n = make_idesc_tf32(128, d.nout), idesc_2n = make_idesc_tf32(128, 2 * d.nout);
       const uint32_t b_lbo = (uint32_t)d.nout * 2 * 16;
@@ -291,6 +321,20 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
         for (int k = 0; k < 3; ++k) atomicAdd(&wu_prof[4 + k], (unsigned long long)pc[k]);
         atomicAdd(&wu_prof[7], (unsigned long long)(clock64() - t_start));
       }
+    }
+  }
+  else if (TMA && warp == WU_TMA_WARP && lane == 0) {
+    // ============================================================ TMA loader
+    const int boxes = (d.ncols + WU_BOXC - 1) / WU_BOXC;   // 1 or 2
+    const uint32_t bytes = (uint32_t)(boxes * WU_ROWS * WU_BOXC + WU_ROWS * d.nout) * 4u;
+    for (int st = 0; st < n_stages; ++st) {
+      const int rs = st % WU_RS;
+      const int r0 = (int)(r_begin + (int64_t)st * WU_ROWS);
+      uint8_t* slot = raw + (size_t)rs * WU_RAW;
+      wu_wait<20>(&raw_empty[rs], ((st / WU_RS) & 1) ^ 1);
+      mbar_arrive_expect_tx(&raw_full[rs], bytes);
+      for (int b = 0; b < boxes; ++b) wu_tma_load_2d(slot + b * (WU_ROWS * WU_BOXC * 4), &map_x, d.col0 + b * WU_BOXC, r0, &raw_full[rs]);
+      wu_tma_load_2d(slot + WU_RAWX, &map_y, 0, r0, &raw_full[rs]);
     }
   }
   __syncthreads();
@@ -428,6 +472,30 @@ int64_t wu_plan(const EegLayout* lin, const EegLayout* lout, const int64_t* w_of
 
 }  // namespace
 
+typedef CUresult (*WuEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// cuTensorMapEncodeTiled through the runtime (no link-time dependency on libcuda); nullptr when the driver does not offer it
+static WuEncodeFn wu_encoder() {
+  static WuEncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    (void)cudaGetLastError();
+    return reinterpret_cast<WuEncodeFn>(p);
+  }();
+  return fn;
+}
+// row-major fp32 matrix [rows][cols] with `pitch` floats between rows, loaded in [WU_ROWS x box_cols] boxes, zero fill outside
+static bool wu_make_map(CUtensorMap* map, const float* base, int64_t rows, int cols, int64_t pitch, int box_cols) {
+  WuEncodeFn enc = wu_encoder();
+  if (enc == nullptr) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows}, strides[1] = {(cuuint64_t)pitch * 4};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)WU_ROWS}, estr[2] = {1, 1};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // Workspace floats of the tensor-core weight gradient, -1 when the shape is outside it (eeg_bwd.cu sizes its workspace with this).
 int64_t eeg_wgrad_umma_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t N) {
   return wu_plan(lin, lout, nullptr, nullptr, N, nullptr, nullptr, nullptr);
@@ -446,14 +514,28 @@ int eeg_wgrad_umma_launch(const float* x, const EegLayout* lin, const float* dy,
   P.prof = prof_on;
   static EegDevFlags attr_dev; bool& attr_set = eeg_dev_flag(attr_dev);
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_wgrad_umma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WU_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(k_wgrad_umma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WU_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_wgrad_umma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)WU_SMEM);
     if (e != cudaSuccess) {
       eeg_set_error("eeg_block_linear_wgrad (tcgen05): cannot opt in to %u B shared memory: %s", WU_SMEM, cudaGetErrorString(e));
       return 2;
     }
     attr_set = true;
   }
-  k_wgrad_umma<<<(unsigned)ctas, WU_THREADS, WU_SMEM, stream>>>(x, dy, ws, P);
+  // one irrep block with one row per node: x and dy are 2-D matrices -> tensor-map (TMA) loads; EEG_WGRAD_TMA=0 forces cp.async
+  static const bool tma_off = getenv("EEG_WGRAD_TMA") && atoi(getenv("EEG_WGRAD_TMA")) == 0;
+  alignas(64) CUtensorMap map_x, map_y;
+  memset(&map_x, 0, sizeof(map_x));
+  memset(&map_y, 0, sizeof(map_y));
+  int nb = 0, b0 = 0;
+  for (int b = 0; b < lin->n_blocks; ++b)
+    if (lin->mul[b] > 0 && lout->mul[b] > 0) { ++nb; b0 = b; }
+  bool tma = !tma_off && nb == 1 && lin->rows[b0] == 1;
+  if (tma)
+    tma = wu_make_map(&map_x, x + lin->off[b0], N, lin->mul[b0], lin->stride, WU_BOXC) &&
+          wu_make_map(&map_y, dy + lout->off[b0], N, lout->mul[b0], lout->stride, lout->mul[b0]);
+  if (tma) k_wgrad_umma<true><<<(unsigned)ctas, WU_THREADS, WU_SMEM, stream>>>(x, dy, ws, P, map_x, map_y);
+  else k_wgrad_umma<false><<<(unsigned)ctas, WU_THREADS, WU_SMEM, stream>>>(x, dy, ws, P, map_x, map_y);
   EEG_CHECK_LAUNCH("eeg_block_linear_wgrad (tcgen05)");
   k_wu_reduce<<<(unsigned)((elems + 31) / 32), dim3(32, 32), 0, stream>>>(ws, dW, P, elems);
   EEG_CHECK_LAUNCH("eeg_block_linear_wgrad (tcgen05 reduce)");

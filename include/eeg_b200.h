@@ -141,7 +141,8 @@ int eeg_pool_tail_fwd(const float* o, const EegLayout* lo, const int32_t* graph_
  * n_weights = floats of dW.  ws: workspace of eeg_block_linear_wgrad_ws_floats(lin, lout, n_weights, bias columns, N) floats ->
  * DETERMINISTIC (row slices are written to ws and added in slice order); ws NULL -> atomicAdd per slice (order varies).
  * With a workspace, 64 output columns and >= 128 weight rows per block (the last radial-MLP layer) the sums run on tcgen05
- * (3xTF32, accumulators drained every <= 512 rows: csrc/eeg_wgrad_umma.cu); EEG_WGRAD=cuda keeps the CUDA-core kernel. */
+ * (3xTF32, accumulators drained every <= 512 rows, operands by tensor-map TMA loads when x and dy are 2-D matrices:
+ * csrc/eeg_wgrad_umma.cu); EEG_WGRAD=cuda keeps the CUDA-core kernel, EEG_WGRAD_TMA=0 the cp.async loads. */
 int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout,
                            const int64_t* host_w_off, const float* host_scale, int transB, const int32_t* in_ld,
                            const int32_t* k_override, float* dW, float* dbias, int64_t N, int64_t n_weights, float* ws,
