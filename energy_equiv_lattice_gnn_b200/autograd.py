@@ -170,6 +170,12 @@ def backward_impl(model, batch, sv, dC) -> List[torch.Tensor]:
         grads[id(inter.linear_up.weight)] = nv.linear_wgrad(sv["h_in"][i], lay_in, dhup, lay_in, uoff, [sC] * nb_in, Wu.numel(), N)[0]
         dh_in = nv.block_linear(dhup, lay_in, Wu, uoff, [sC] * nb_in, lay_in, N, transB=True)
         dh = dh_in + dh if i > 0 else dh_in   # residual of layer i > 0 (gnn/model.py:95-96)
+        if i == 1:
+            # every parameter outside layer 0 and the node embedding has its final gradient: a data-parallel trainer can start
+            # reducing those now, under the layer-0 backward (train.Trainer._early_bucket pops what it takes from `grads`)
+            hook = model.__dict__.get("_grads_ready_hook")
+            if hook is not None:
+                hook(grads)
     # ---- node embedding: h0[n, c] = a[n] W[c] + b[c]
     emb = model.node_ft_embedding
     a = batch.node_attrs.to(torch.float32).reshape(-1).contiguous()

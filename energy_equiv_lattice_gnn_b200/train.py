@@ -114,7 +114,7 @@ class Trainer:
     of unequal size (sharding.shard_batch) still give the gradient of the global-mean loss."""
 
     def __init__(self, model, lr=1e-3, beta1=0.9, eps=1e-8, weight_decay=1e-8, amsgrad=True, clip_norm=10.0, process_group=None,
-                 accumulate_grad_batches: int = 1, global_mean: bool = False):
+                 accumulate_grad_batches: int = 1, global_mean: bool = False, overlap_allreduce: bool = True):
         self.model = model
         self.opt = FlatAdamW(model, lr=lr, beta1=beta1, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad, clip_norm=clip_norm)
         self.pg = process_group
@@ -122,10 +122,33 @@ class Trainer:
         self.global_mean = bool(global_mean)
         self._micro = 0
         self._count = None   # graphs accumulated since the last optimizer step (global_mean only)
+        # Overlap of the gradient all-reduce with the backward: the parameters are laid out [node embedding, layer 0, layer 1 ...,
+        # readout, final linear]; everything from layer 1 on (79 % of the default model's gradient) is final when the backward
+        # enters layer 0, so that tail of the flat buffer is all-reduced asynchronously under the layer-0 backward and only
+        # the head is reduced after it.
+        self.overlap_allreduce = bool(overlap_allreduce)
+        names = [n for n, p in model.named_parameters() if p.requires_grad]
+        head = [n.startswith("node_ft_embedding.") or n.startswith("stiffness_head.layers.0.") for n in names]
+        self._tail_idx = head.index(False) if False in head else len(head)
+        if any(head[self._tail_idx:]) or self._tail_idx == 0:
+            self._tail_idx = len(head)          # unexpected parameter order: no overlap
+        self._tail_off = self.opt.slices[self._tail_idx][0] if self._tail_idx < len(head) else self.opt.grad.numel()
+        self._pending = None
 
     def _distributed(self) -> bool:
         return torch.distributed.is_available() and torch.distributed.is_initialized() and \
             torch.distributed.get_world_size(self.pg) > 1
+
+    def _early_bucket(self, grads) -> None:
+        """Called by the explicit backward (autograd.backward_impl) once every gradient outside layer 0 / the node embedding is
+        final: add them into the flat buffer (what autograd's accumulation would do after the backward), take them out of
+        `grads` so that they are not added twice, and start the all-reduce of that part of the buffer."""
+        for p, (off, k) in zip(self.opt.params[self._tail_idx:], self.opt.slices[self._tail_idx:]):
+            g = grads.pop(id(p), None)
+            if g is not None:
+                self.opt.grad[off:off + k].add_(g.reshape(-1))
+        self._pending = torch.distributed.all_reduce(self.opt.grad[self._tail_off:], op=torch.distributed.ReduceOp.SUM, group=self.pg,
+                                                     async_op=True)
 
     def training_step(self, batch) -> torch.Tensor:
         self.model.train()
@@ -136,7 +159,14 @@ class Trainer:
         n_local = float(out.shape[0])
         # global_mean: back-propagate the SUM over this rank's lattices; divided by the global count at the step
         scaled = loss * (n_local if self.global_mean else 1.0 / self.accumulate)
-        scaled.backward()
+        early = (self.overlap_allreduce and not self.global_mean and self._micro == self.accumulate - 1 and self._distributed()
+                 and self._tail_off < self.opt.grad.numel())
+        if early:
+            self.model._grads_ready_hook = self._early_bucket
+        try:
+            scaled.backward()
+        finally:
+            self.model.__dict__.pop("_grads_ready_hook", None)
         self.opt.gather_grads()
         if self.global_mean:
             c = torch.tensor([n_local], dtype=torch.float64, device=out.device)
@@ -145,7 +175,12 @@ class Trainer:
         if self._micro < self.accumulate:
             return loss.detach()
         self._micro = 0
-        world = sync_gradients(self.opt.grad, self.pg)
+        if self._pending is not None:           # the tail is already in flight: reduce the head, then join
+            world = sync_gradients(self.opt.grad[:self._tail_off], self.pg)
+            self._pending.wait()
+            self._pending = None
+        else:
+            world = sync_gradients(self.opt.grad, self.pg)
         if self.global_mean:
             if self._distributed():
                 torch.distributed.all_reduce(self._count, op=torch.distributed.ReduceOp.SUM, group=self.pg)
