@@ -165,6 +165,10 @@ int eeg_lin32_mma_launch(const float* in, const EegLayout* lin, const float* W, 
                          const float* bias, int transB, const float* residual, float* out, const EegLayout* lout, int64_t N,
                          cudaStream_t stream);
 
+// long-K, 64-output input gradient on tcgen05 with TMA operands (eeg_dx_umma.cu): 0 = launched, -1 = shape outside it
+int eeg_dx_umma_launch(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off, const float* host_scale,
+                       int transB, float* out, const EegLayout* lout, int64_t N, cudaStream_t stream);
+
 static bool eeg_linear_use_tc() {
   static const char* env = getenv("EEG_LINEAR");  // "cuda": force the CUDA-core GEMM (A/B timing, debugging)
   return !(env && !strcmp(env, "cuda"));
@@ -236,6 +240,10 @@ extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const
                                           nullptr, nullptr, (cudaStream_t)stream);
       if (rc != -1) return rc;
     }
+  }
+  if (act == 0 && bias == nullptr && residual == nullptr && eeg_linear_use_tc()) {
+    const int rd = eeg_dx_umma_launch(in, lin, W, host_w_off, host_scale, transB, out, lout, N, (cudaStream_t)stream);
+    if (rd != -1) return rd;
   }
   LinearParams P;
   P.n_blocks = lin->n_blocks;

@@ -24,11 +24,11 @@
 // Measured alternatives (radial-MLP shape, 512 lattices; the CUDA-core kernel takes 0.475 ms):
 //   per-thread LDG.32 straight into registers: 2.6 warp instructions per element of address arithmetic, 0.23 ms;
 //   one cp.async.bulk per row (2 KB / 256 B) from a loader warp: ~110 clk per bulk copy whatever its size, 0.19-0.22 ms.
-#include <cuda.h>   // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint, libcuda is not linked)
 #include <stdlib.h>
 #include <string.h>
 #include "eeg_common.cuh"
 #include "eeg_umma.cuh"
+#include "eeg_tma.cuh"
 
 namespace {
 using namespace eeg_umma;
@@ -93,14 +93,6 @@ __device__ __forceinline__ float wu_hi(float x) { return __uint_as_float((__floa
 // barrier, [1] waiting for a free operand stage, [2] transforming, [3] draining; of the MMA lane in [4] waiting for operands,
 // [5] issuing, [6] waiting for the drain; [7] whole kernel.
 __device__ unsigned long long wu_prof[8];
-
-// 2-D tiled TMA load (cp.async.bulk.tensor): box (c0.., r0..) of the tensor map -> dense [box rows][box cols] in shared memory
-__device__ __forceinline__ void wu_tma_load_2d(void* smem_dst, const CUtensorMap* map, int c0, int r0, uint64_t* bar) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-                   smem_u32(smem_dst)),
-               "l"(map), "r"(c0), "r"(r0), "r"(smem_u32(bar))
-               : "memory");
-}
 
 // TMA = true (one irrep block with one row per node: x and dy are plain 2-D row-major matrices, the radial-MLP case): a loader
 // warp issues three tensor-map loads per stage (two [8 x 256] boxes of x, one [8 x nout] box of dy; rows and columns past the
@@ -333,8 +325,8 @@ k_wgrad_umma(const float* __restrict__ x, const float* __restrict__ dy, float* _
       uint8_t* slot = raw + (size_t)rs * WU_RAW;
       wu_wait<20>(&raw_empty[rs], ((st / WU_RS) & 1) ^ 1);
       mbar_arrive_expect_tx(&raw_full[rs], bytes);
-      for (int b = 0; b < boxes; ++b) wu_tma_load_2d(slot + b * (WU_ROWS * WU_BOXC * 4), &map_x, d.col0 + b * WU_BOXC, r0, &raw_full[rs]);
-      wu_tma_load_2d(slot + WU_RAWX, &map_y, 0, r0, &raw_full[rs]);
+      for (int b = 0; b < boxes; ++b) eeg_tma::load_2d(slot + b * (WU_ROWS * WU_BOXC * 4), &map_x, d.col0 + b * WU_BOXC, r0, &raw_full[rs]);
+      eeg_tma::load_2d(slot + WU_RAWX, &map_y, 0, r0, &raw_full[rs]);
     }
   }
   __syncthreads();
@@ -472,30 +464,6 @@ int64_t wu_plan(const EegLayout* lin, const EegLayout* lout, const int64_t* w_of
 
 }  // namespace
 
-typedef CUresult (*WuEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                               const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-// cuTensorMapEncodeTiled through the runtime (no link-time dependency on libcuda); nullptr when the driver does not offer it
-static WuEncodeFn wu_encoder() {
-  static WuEncodeFn fn = [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
-      p = nullptr;
-    (void)cudaGetLastError();
-    return reinterpret_cast<WuEncodeFn>(p);
-  }();
-  return fn;
-}
-// row-major fp32 matrix [rows][cols] with `pitch` floats between rows, loaded in [WU_ROWS x box_cols] boxes, zero fill outside
-static bool wu_make_map(CUtensorMap* map, const float* base, int64_t rows, int cols, int64_t pitch, int box_cols) {
-  WuEncodeFn enc = wu_encoder();
-  if (enc == nullptr) return false;
-  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows}, strides[1] = {(cuuint64_t)pitch * 4};
-  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)WU_ROWS}, estr[2] = {1, 1};
-  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 // Workspace floats of the tensor-core weight gradient, -1 when the shape is outside it (eeg_bwd.cu sizes its workspace with this).
 int64_t eeg_wgrad_umma_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t N) {
   return wu_plan(lin, lout, nullptr, nullptr, N, nullptr, nullptr, nullptr);
@@ -532,8 +500,8 @@ int eeg_wgrad_umma_launch(const float* x, const EegLayout* lin, const float* dy,
     if (lin->mul[b] > 0 && lout->mul[b] > 0) { ++nb; b0 = b; }
   bool tma = !tma_off && nb == 1 && lin->rows[b0] == 1;
   if (tma)
-    tma = wu_make_map(&map_x, x + lin->off[b0], N, lin->mul[b0], lin->stride, WU_BOXC) &&
-          wu_make_map(&map_y, dy + lout->off[b0], N, lout->mul[b0], lout->stride, lout->mul[b0]);
+    tma = eeg_tma::make_map_2d(&map_x, x + lin->off[b0], N, lin->mul[b0], lin->stride, WU_BOXC, WU_ROWS) &&
+          eeg_tma::make_map_2d(&map_y, dy + lout->off[b0], N, lout->mul[b0], lout->stride, lout->mul[b0], WU_ROWS);
   if (tma) k_wgrad_umma<true><<<(unsigned)ctas, WU_THREADS, WU_SMEM, stream>>>(x, dy, ws, P, map_x, map_y);
   else k_wgrad_umma<false><<<(unsigned)ctas, WU_THREADS, WU_SMEM, stream>>>(x, dy, ws, P, map_x, map_y);
   EEG_CHECK_LAUNCH("eeg_block_linear_wgrad (tcgen05)");

@@ -141,3 +141,21 @@ def test_wide_weight_gradient_on_tensor_cores(cuda_device, rows, k_in, R):
         ref = scale[b] * xb.t() @ yb
         assert rel(got[w_off[b]:w_off[b] + k * 64].view(k, 64), ref) < 1e-5
     assert rel(gb, dy[:, :64].double().sum(0)) < 1e-5
+
+
+@pytest.mark.parametrize("K,R", [(1344, 20003), (192, 30001), (2048, 4099)])
+def test_long_k_input_gradient_on_tensor_cores(cuda_device, K, R):
+    """eeg_block_linear_fwd with one block, one row per node, K >= 128 and 64 outputs (ds = dw W2 of the radial-MLP backward,
+    gnn/blocks.py:538-549) runs on tcgen05 with TMA-loaded operands (csrc/eeg_dx_umma.cu): against torch fp64 at 1e-5 of the
+    max, bitwise repeatable, row counts that are not multiples of the 512-row CTA tile, one to four accumulation passes, and
+    an output row pitch wider than the 64 columns written."""
+    g = torch.Generator().manual_seed(11 + K)
+    lin = nv.make_layout([1], [K])
+    lout = nv.make_layout([1], [64])
+    x = torch.randn(R, K, generator=g).to(cuda_device)
+    W = torch.randn(K, 64, generator=g).to(cuda_device)
+    got = nv.block_linear(x, lin, W.reshape(-1), [0], [0.25], lout, R)
+    again = nv.block_linear(x, lin, W.reshape(-1), [0], [0.25], lout, R)
+    assert torch.equal(got, again)
+    ref = 0.25 * x.double() @ W.double()
+    assert rel(got, ref) < 1e-5
