@@ -53,6 +53,20 @@ def _static(model, name, build):
 
 def _mlp_backward(lins: List[torch.nn.Linear], f, dw, E, lay_f, lay_h, lay_w, grads):
     """conv_tp_weights MLP (gnn/blocks.py:538-549): activations are recomputed, then dW / db layer by layer."""
+    F = lay_f.mul[0]
+    if (len(lins) == 3 and lins[0].out_features == 64 and lins[1].in_features == 64 and lins[1].out_features == 64 and F % 4 == 0
+            and F <= 32 and lins[0].in_features == F and lins[0].bias is not None and lins[1].bias is not None):
+        # default shape: ds2 on tcgen05 (eeg_dx_umma.cu), the two hidden layers in one fused pass (eeg_radial_bwd.cu) which also
+        # returns s2 = silu(a2), then the last layer's weight gradient on tcgen05 (eeg_wgrad_umma.cu)
+        last = lins[-1]
+        W2 = last.weight.detach()
+        ds2 = nv.block_linear(dw, lay_w, W2.reshape(-1), [0], [1.0], lay_h, E)
+        s2, dW0, db0, dW1, db1 = nv.radial_hidden_bwd(f, F, lins[0].weight.detach(), lins[0].bias.detach(), lins[1].weight.detach(),
+                                                      lins[1].bias.detach(), ds2, E)
+        grads[id(lins[0].weight)], grads[id(lins[0].bias)] = dW0, db0
+        grads[id(lins[1].weight)], grads[id(lins[1].bias)] = dW1, db1
+        grads[id(last.weight)] = nv.linear_wgrad(dw, lay_w, s2, lay_h, [0], [1.0], W2.numel(), E)[0].view_as(W2)
+        return
     pre, act = [], [f]
     lay_in = lay_f
     for lin in lins[:-1]:

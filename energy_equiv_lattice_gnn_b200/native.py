@@ -24,7 +24,7 @@ SYMBOLS = [
     "eeg_tp_scatter_bwd", "eeg_sym_contract_bwd_x", "eeg_sc_coef_grad", "eeg_sc_coefficients_bwd", "eeg_sc_grad_slices",
     "eeg_sumsq", "eeg_adamw_step", "eeg_rotate_vec3", "eeg_rotate_cart4_to_mandel", "eeg_validation_metrics", "eeg_scale_rows_inv_degree",
     "eeg_collate_gather", "eeg_rand_rotations", "eeg_tp_scatter_umma_fwd", "eeg_segment_sum_rows",
-    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd", "eeg_blocks32_transpose", "eeg_graph_validate",
+    "eeg_block_linear_wgrad_ws_floats", "eeg_radial_embedding_fwd", "eeg_blocks32_transpose", "eeg_graph_validate", "eeg_radial_hidden_bwd", "eeg_radial_hidden_bwd_ws_floats",
 ]
 
 
@@ -377,6 +377,24 @@ def linear_wgrad(x, lin: EegLayout, dy, lout: EegLayout, w_off, scale, n_weights
                                     C.c_int64(n_weights), _p(ws), C.c_int64(ws.numel()), _stream()),
            "eeg_block_linear_wgrad")
     return dW, db
+
+
+def radial_hidden_bwd(f, F: int, W0, b0, W1, b1, ds2, E: int):
+    """Fused backward of Linear(F,64)-SiLU-Linear(64,64)-SiLU: -> (s2 [E,64], dW0 [64,F], db0 [64], dW1 [64,64], db1 [64])."""
+    dev = f.device
+    s2 = torch.empty(E, 64, dtype=f32, device=dev)
+    dW0 = torch.zeros(64, F, dtype=f32, device=dev)
+    db0 = torch.zeros(64, dtype=f32, device=dev)
+    dW1 = torch.zeros(64, 64, dtype=f32, device=dev)
+    db1 = torch.zeros(64, dtype=f32, device=dev)
+    L = lib()
+    L.eeg_radial_hidden_bwd_ws_floats.restype = C.c_int64
+    ws = torch.empty(max(int(L.eeg_radial_hidden_bwd_ws_floats(C.c_int(F), C.c_int64(E))), 1), dtype=f32, device=dev)
+    _begin("eeg_radial_hidden_bwd")
+    _check(L.eeg_radial_hidden_bwd(_p(f, f32), C.c_int(F), C.c_int(f.shape[1]), _p(W0, f32), _p(b0, f32), _p(W1, f32), _p(b1, f32),
+                                   _p(ds2, f32), C.c_int64(E), _p(s2), _p(dW0), _p(db0), _p(dW1), _p(db1), _p(ws), C.c_int64(ws.numel()),
+                                   _stream()), "eeg_radial_hidden_bwd")
+    return s2, dW0, db0, dW1, db1
 
 
 def colsum(x, row_scale=None):

@@ -148,6 +148,16 @@ int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, const float* dy
                            const int32_t* k_override, float* dW, float* dbias, int64_t N, int64_t n_weights, float* ws,
                            int64_t ws_floats, void* stream);
 int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t n_weights, int bias_cols, int64_t N);
+
+/* Backward of the two hidden layers of the radial MLP (gnn/blocks.py:538-549: Linear(F,64) - SiLU - Linear(64,64) - SiLU) in one
+ * pass over the edges: given the edge features f [E, f_stride] (first F columns), the torch.nn.Linear weights W0 [64,F], b0,
+ * W1 [64,64], b1 and ds2 = dL/d(silu(a2)) [E,64], recomputes the activations and adds dW0 [64,F], db0, dW1 [64,64], db1 (+=:
+ * zero them first); s2_out [E,64] (may be NULL) receives silu(a2), the input of the last linear, for its weight gradient.
+ * F a multiple of 4, <= 32.  Deterministic: per-CTA partials in ws (eeg_radial_hidden_bwd_ws_floats floats), fixed-order sum. */
+int eeg_radial_hidden_bwd(const float* f, int F, int f_stride, const float* W0, const float* b0, const float* W1, const float* b1,
+                          const float* ds2, int64_t E, float* s2_out, float* dW0, float* db0, float* dW1, float* db1, float* ws,
+                          int64_t ws_floats, void* stream);
+int64_t eeg_radial_hidden_bwd_ws_floats(int F, int64_t E);
 /* out[c] += sum_r row_scale[r] * x[r*ld + c]   (row_scale may be NULL = 1): bias / embedding gradients.
  * ws: ceil(R / 256) * cols floats -> deterministic (CTA partials added in order); NULL -> atomicAdd. */
 int eeg_colsum(const float* x, int64_t R, int ld, int cols, const float* row_scale, float* out, float* ws, int64_t ws_floats,
