@@ -107,16 +107,29 @@ __global__ void __launch_bounds__(WG_WARPS * 32, 1) k_sc_wgrad(const float* __re
     if (seg * SEG + k < NCOEF) o[(int64_t)k * C] = A[k];
 }
 
-// slice 0 <- sum over slices (fixed order), float4 per thread
-__global__ void k_sc_slice_sum(float4* __restrict__ dT, int64_t n4, int n_slices) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n4) return;
-  float4 s = dT[e];
-  for (int z = 1; z < n_slices; ++z) {
-    const float4 v = dT[z * n4 + e];
-    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+// slice 0 <- sum over slices in a fixed order: block = 32 float4 elements x 8 partial lanes (lane y adds slices y, y + 8, ...;
+// the lane sums are added in lane order).  One thread per element chained n_slices dependent loads.
+__global__ void __launch_bounds__(256) k_sc_slice_sum(float4* __restrict__ dT, int64_t n4, int n_slices) {
+  __shared__ float4 part[8][33];
+  const int64_t e = (int64_t)blockIdx.x * 32 + threadIdx.x;
+  const int y = threadIdx.y;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (e < n4)
+    for (int z = y; z < n_slices; z += 8) {
+      const float4 v = dT[z * n4 + e];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+  part[y][threadIdx.x] = s;
+  __syncthreads();
+  if (y == 0 && e < n4) {
+    float4 r = part[0][threadIdx.x];
+#pragma unroll
+    for (int q = 1; q < 8; ++q) {
+      const float4 v = part[q][threadIdx.x];
+      r.x += v.x; r.y += v.y; r.z += v.z; r.w += v.w;
+    }
+    dT[e] = r;
   }
-  dT[e] = s;
 }
 
 __global__ void k_sc_coefficients_bwd(const int32_t* __restrict__ tp, const int32_t* __restrict__ trow, const float* __restrict__ tval,
@@ -176,7 +189,7 @@ extern "C" int eeg_sc_coefficients_bwd(const int32_t* t_ptr, const int32_t* t_ro
   if (n_wrows == 0 || n_coef == 0) return 0;
   EEG_REQUIRE(C % 4 == 0, "eeg_sc_coefficients_bwd: C must be a multiple of 4");
   const int64_t n4 = (int64_t)n_coef * C / 4;
-  k_sc_slice_sum<<<eeg_div_up(n4, 256), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(dT), n4, eeg_sc_grad_slices());
+  k_sc_slice_sum<<<eeg_div_up(n4, 32), dim3(32, 8), 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(dT), n4, eeg_sc_grad_slices());
   EEG_CHECK_LAUNCH("eeg_sc_coefficients_bwd(slice sum)");
   dim3 block(32, 4), grid(eeg_div_up(n_wrows, 4));
   k_sc_coefficients_bwd<<<grid, block, 0, (cudaStream_t)stream>>>(t_ptr, t_row, t_val, n_wrows, dT, C, dW);
