@@ -169,6 +169,10 @@ int eeg_lin32_mma_launch(const float* in, const EegLayout* lin, const float* W, 
 int eeg_dx_umma_launch(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off, const float* host_scale,
                        int transB, float* out, const EegLayout* lout, int64_t N, cudaStream_t stream);
 
+// multiplicity 32 -> wide outputs on warp MMAs (eeg_lin32wide.cu): 0 = launched, -1 = shape outside it
+int eeg_lin32_wide_launch(const float* in, const EegLayout* lin, const float* W, const int64_t* host_w_off, const float* host_scale,
+                          int transB, float* out, const EegLayout* lout, int64_t N, cudaStream_t stream);
+
 static bool eeg_linear_use_tc() {
   static const char* env = getenv("EEG_LINEAR");  // "cuda": force the CUDA-core GEMM (A/B timing, debugging)
   return !(env && !strcmp(env, "cuda"));
@@ -216,6 +220,10 @@ extern "C" int eeg_block_linear_fwd(const float* in, const EegLayout* lin, const
     // multiplicity-32 inputs: node-major warp-level tensor-core kernel (eeg_lin32mma.cu)
     const int rm = eeg_lin32_mma_launch(in, lin, W, host_w_off, host_scale, bias, transB, residual, out, lout, N, (cudaStream_t)stream);
     if (rm != -1) return rm;
+    if (bias == nullptr && residual == nullptr) {
+      const int rw = eeg_lin32_wide_launch(in, lin, W, host_w_off, host_scale, transB, out, lout, N, (cudaStream_t)stream);
+      if (rw != -1) return rw;
+    }
   }
   if (act == 0 && env32 && !strcmp(env32, "lin32")) {
     // measured on B200 (N = 30720): 107 / 102 us (product+residual / linear_1) vs 101 / 96 us on the tiled GEMM below, so

@@ -183,3 +183,28 @@ def test_fused_radial_hidden_backward(cuda_device, F, E):
     assert rel(got[0], s2.detach()) < 1e-5
     for a, ref in zip(got[1:], p):
         assert rel(a, ref.grad) < 1e-5
+
+
+def test_wide_output_linear_from_multiplicity_32(cuda_device):
+    """eeg_block_linear_fwd, multiplicity 32 -> 160..352 columns per irrep block (dM = dmsg W^T of the interaction.linear backward,
+    gnn/blocks.py:552-559) runs on warp MMAs (csrc/eeg_lin32wide.cu): both weight layouts against torch fp64 at 1e-5, a node
+    count that leaves partial 16-row tiles, bitwise repeatable."""
+    g = torch.Generator().manual_seed(3)
+    N, rows, nout = 1037, [1, 3, 5, 7, 9], [160, 256, 352, 32, 288]
+    lin, lout = nv.make_layout(rows, [32] * 5), nv.make_layout(rows, nout)
+    x = torch.randn(N, lin.stride, generator=g).to(cuda_device)
+    w_off, n_w = [], 0
+    for n in nout:
+        w_off.append(n_w)
+        n_w += 32 * n
+    W = torch.randn(n_w, generator=g).to(cuda_device)
+    scale = [0.3, 0.5, 0.7, 1.1, 1.3]
+    for transB in (True, False):
+        got = nv.block_linear(x, lin, W, w_off, scale, lout, N, transB=transB)
+        assert torch.equal(got, nv.block_linear(x, lin, W, w_off, scale, lout, N, transB=transB))
+        for b, (r, n) in enumerate(zip(rows, nout)):
+            Wb = W[w_off[b]:w_off[b] + 32 * n].double()
+            Wb = Wb.view(n, 32).t() if transB else Wb.view(32, n)
+            xin = x[:, lin.off[b]:lin.off[b] + r * 32].reshape(N * r, 32).double()
+            ref = scale[b] * xin @ Wb
+            assert rel(got[:, lout.off[b]:lout.off[b] + r * n].reshape(N * r, n), ref) < 1e-5
