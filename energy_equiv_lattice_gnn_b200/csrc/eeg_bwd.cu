@@ -463,11 +463,22 @@ static bool wg_use_tc() {
   static const char* env = getenv("EEG_WGRAD");   // "cuda": keep every weight gradient on the CUDA-core kernel (A/B timing)
   return !(env && !strcmp(env, "cuda"));
 }
-// workspace of the tensor-core path incl. the bias partials behind it; -1 when the call cannot take that path
-static int64_t wg_umma_need(const EegLayout* lin, const EegLayout* lout, int bias_cols, int64_t N, int64_t* bias_need) {
+// warp-MMA path for 32 output channels (eeg_wgrad_mma.cu)
+int64_t eeg_wgrad_mma_ws_floats(const EegLayout* lin, const EegLayout* lout, int64_t N);
+int eeg_wgrad_mma_launch(const float* x, const EegLayout* lin, const float* dy, const EegLayout* lout, const int64_t* host_w_off,
+                         const float* host_scale, int transB, float* dW, int64_t N, float* ws, int64_t ws_floats, cudaStream_t stream);
+// workspace of a tensor-core path (*which = 1: tcgen05, 2: warp MMA) incl. the bias partials behind it; -1 when the call cannot
+// take either
+static int64_t wg_umma_need(const EegLayout* lin, const EegLayout* lout, int bias_cols, int64_t N, int64_t* bias_need, int* which) {
   *bias_need = 0;
+  *which = 0;
   if (!wg_use_tc()) return -1;
-  const int64_t un = eeg_wgrad_umma_ws_floats(lin, lout, N);
+  int64_t un = eeg_wgrad_umma_ws_floats(lin, lout, N);
+  *which = 1;
+  if (un < 0) {
+    un = eeg_wgrad_mma_ws_floats(lin, lout, N);
+    *which = 2;
+  }
   if (un < 0) return -1;
   if (bias_cols > 0) {
     if (lin->rows[0] != 1 || lout->mul[0] != bias_cols) return -1;
@@ -484,9 +495,11 @@ extern "C" int eeg_block_linear_wgrad(const float* x, const EegLayout* lin, cons
   if (N == 0) return 0;
   if (ws != nullptr && in_ld == nullptr && k_override == nullptr) {
     int64_t bias_need = 0;
-    const int64_t un = wg_umma_need(lin, lout, dbias ? lout->mul[0] : 0, N, &bias_need);
+    int which = 0;
+    const int64_t un = wg_umma_need(lin, lout, dbias ? lout->mul[0] : 0, N, &bias_need, &which);
     if (un >= 0 && ws_floats >= un + bias_need) {
-      const int rc = eeg_wgrad_umma_launch(x, lin, dy, lout, host_w_off, host_scale, transB, dW, N, ws, un, (cudaStream_t)stream);
+      const int rc = which == 1 ? eeg_wgrad_umma_launch(x, lin, dy, lout, host_w_off, host_scale, transB, dW, N, ws, un, (cudaStream_t)stream)
+                                : eeg_wgrad_mma_launch(x, lin, dy, lout, host_w_off, host_scale, transB, dW, N, ws, un, (cudaStream_t)stream);
       if (rc > 0) return rc;
       if (rc == 0) return dbias ? eeg_colsum(dy + lout->off[0], N, lout->stride, lout->mul[0], nullptr, dbias, ws + un, bias_need, stream) : 0;
     }
@@ -555,7 +568,8 @@ extern "C" int64_t eeg_block_linear_wgrad_ws_floats(const EegLayout* lin, const 
     if (sl > slices) slices = sl;
   }
   int64_t need = slices * (n_weights + bias_cols), bias_need = 0;
-  const int64_t un = lin && lout ? wg_umma_need(lin, lout, bias_cols, N, &bias_need) : -1;
+  int which = 0;
+  const int64_t un = lin && lout ? wg_umma_need(lin, lout, bias_cols, N, &bias_need, &which) : -1;
   if (un >= 0 && un + bias_need > need) need = un + bias_need;
   return need;
 }

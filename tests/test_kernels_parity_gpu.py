@@ -208,3 +208,30 @@ def test_wide_output_linear_from_multiplicity_32(cuda_device):
             xin = x[:, lin.off[b]:lin.off[b] + r * 32].reshape(N * r, 32).double()
             ref = scale[b] * xin @ Wb
             assert rel(got[:, lout.off[b]:lout.off[b] + r * n].reshape(N * r, n), ref) < 1e-5
+
+
+def test_weight_gradient_32_outputs_on_warp_mma(cuda_device):
+    """eeg_block_linear_wgrad with 32 output channels and K = 64..352 per block (path-stacked interaction.linear,
+    gnn/blocks.py:552-559) runs on mma.sync (csrc/eeg_wgrad_mma.cu): against torch fp64 at 1e-5, with a bias gradient, a row
+    count that leaves partial 8-row K-steps and partial 512-row slices, both weight layouts, bitwise repeatable."""
+    g = torch.Generator().manual_seed(17)
+    N, rows, k_in = 6007, [1, 3, 5, 7, 9], [160, 256, 352, 64, 288]
+    lin, lout = nv.make_layout(rows, k_in), nv.make_layout(rows, [32] * 5)
+    x = torch.randn(N, lin.stride, generator=g).to(cuda_device)
+    dy = torch.randn(N, lout.stride, generator=g).to(cuda_device)
+    w_off, n_w = [], 0
+    for k in k_in:
+        w_off.append(n_w)
+        n_w += k * 32
+    scale = [0.3, 0.5, 0.7, 1.1, 1.3]
+    for transB in (False, True):
+        got, gb = nv.linear_wgrad(x, lin, dy, lout, w_off, scale, n_w, N, transB=transB, want_bias=32)
+        again, gb2 = nv.linear_wgrad(x, lin, dy, lout, w_off, scale, n_w, N, transB=transB, want_bias=32)
+        assert torch.equal(got, again) and torch.equal(gb, gb2)
+        for b, (r, k) in enumerate(zip(rows, k_in)):
+            xb = x[:, lin.off[b]:lin.off[b] + r * k].reshape(N * r, k).double()
+            yb = dy[:, lout.off[b]:lout.off[b] + r * 32].reshape(N * r, 32).double()
+            ref = scale[b] * xb.t() @ yb
+            gotb = got[w_off[b]:w_off[b] + k * 32]
+            assert rel(gotb.view(32, k).t() if transB else gotb.view(k, 32), ref) < 1e-5
+        assert rel(gb, dy[:, :32].double().sum(0)) < 1e-5
