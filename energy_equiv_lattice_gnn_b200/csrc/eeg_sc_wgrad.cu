@@ -10,6 +10,7 @@
 //   eeg_sc_coefficients_bwd: dW[k,c] = sum_slot A[slot,k] sum_z dT[z][slot][c]   (transpose of eeg_sc_coefficients); the
 //                            slices are first summed into slice 0 in place (dT is scratch)
 #include "eeg_common.cuh"
+#include "eeg_umma.cuh"   // mbarrier + cp.async.bulk helpers
 #include "generated/all_scw.cuh"
 
 namespace {
@@ -53,9 +54,31 @@ __global__ void __launch_bounds__(WG_WARPS * 32, 1) k_sc_wgrad(const float* __re
   const int64_t n_begin = blockIdx.z * per, n_end = n_begin + per < N ? n_begin + per : N;
   const int n_tiles = n_begin < n_end ? (int)((n_end - n_begin + WG_NB - 1) / WG_NB) : 0;
 
+  // C == 32: a full tile of x (and of dout) is ONE contiguous 25.6 KB block -> one bulk copy (TMA engine) each, issued by one
+  // thread, completion on an mbarrier.  (The per-thread cp.async loop below - 12.5 chunks per thread and tile, each with its
+  // own row / piece arithmetic - was 28 % of the kernel's instructions: profiles/r02_ncu_tp_bwd2_scw_summary.txt.)  Partial
+  // tiles (only the last of a slice) and C > 32 keep the cp.async path with its zero fill.
+  __shared__ uint64_t bulk_bar[2];
+  if (threadIdx.x == 0) {
+    eeg_umma::mbar_init(&bulk_bar[0], 1);
+    eeg_umma::mbar_init(&bulk_bar[1], 1);
+    eeg_umma::mbar_fence_init();
+  }
+  __syncthreads();
+  uint32_t bulk_phase[2] = {0u, 0u};
+  auto is_bulk = [&](int t) { return C == 32 && n_begin + (int64_t)(t + 1) * WG_NB <= n_end; };
   auto stage = [&](int t) {   // tile t: rows (node, d) are consecutive rows of the [N*D, C] matrices; 8 x 16 B per row chunk
     float* dst = wg_smem + (t & 1) * 2 * TILE;
     const int64_t row0 = (n_begin + (int64_t)t * WG_NB) * D, row_end = n_end * D;
+    if (is_bulk(t)) {
+      if (threadIdx.x == 0) {
+        eeg_umma::fence_proxy_async_smem();   // the buffer's previous readers (generic proxy) are behind the barrier of the caller
+        eeg_umma::mbar_arrive_expect_tx(&bulk_bar[t & 1], 2 * TILE * 4);
+        eeg_umma::bulk_g2s(dst, x + row0 * 32, TILE * 4, &bulk_bar[t & 1]);
+        eeg_umma::bulk_g2s(dst + TILE, dout + row0 * 32, TILE * 4, &bulk_bar[t & 1]);
+      }
+      return;
+    }
     for (int e = threadIdx.x; e < 2 * WG_NB * D * 8; e += WG_WARPS * 32) {
       const int which = e >= WG_NB * D * 8, r = (which ? e - WG_NB * D * 8 : e) >> 3, piece = e & 7;
       const bool ok = row0 + r < row_end;
@@ -70,9 +93,12 @@ __global__ void __launch_bounds__(WG_WARPS * 32, 1) k_sc_wgrad(const float* __re
   for (int k = 0; k < SEG; ++k) A[k] = 0.f;
   if (n_tiles > 0) stage(0);
   for (int t = 0; t < n_tiles; ++t) {
-    if (t + 1 < n_tiles) {
-      stage(t + 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    if (t + 1 < n_tiles) stage(t + 1);
+    if (is_bulk(t)) {
+      eeg_umma::mbar_wait(&bulk_bar[t & 1], bulk_phase[t & 1]);
+      bulk_phase[t & 1] ^= 1u;
+    } else if (t + 1 < n_tiles && !is_bulk(t + 1)) {
+      asm volatile("cp.async.wait_group 1;" ::: "memory");   // C > 32: the next tile's copies stay in flight
     } else {
       asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
