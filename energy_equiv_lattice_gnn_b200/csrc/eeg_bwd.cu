@@ -244,9 +244,12 @@ __global__ void k_gate_bwd(const float* __restrict__ z, const float* __restrict_
   const float* gr = dg + n * P.lg.stride;
   float* dr = dz + n * P.lz.stride;
   for (int u = threadIdx.x; u < P.n_scalars; u += blockDim.x) dr[u] = gr[u] * P.c * silu_grad(zr[u]);
-  for (int b = 1; b < P.lz.n_blocks; ++b) {
+  // one warp per gated block (lane = channel): the blocks of a node run side by side instead of one after the other with a
+  // quarter of the CTA active
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  for (int b = 1 + warp; b < P.lz.n_blocks; b += nwarps) {
     const int mul = P.lz.mul[b], rows = P.lz.rows[b];
-    for (int u = threadIdx.x; u < mul; u += blockDim.x) {
+    for (int u = lane; u < mul; u += 32) {
       const float zg = zr[P.gate_off[b] + u];
       const float gv = P.c * eeg_silu(zg);
       float s = 0.f;

@@ -46,6 +46,16 @@ def make_layout(rows: Sequence[int], mul: Sequence[int]) -> EegLayout:
     return lay
 
 
+def sub_layout(lay: EegLayout, blocks: Sequence[int]) -> EegLayout:
+    """The given irrep blocks of `lay` as a layout of their own (same node stride, same offsets inside the node row)."""
+    sub = EegLayout()
+    sub.n_blocks = len(blocks)
+    for q, b in enumerate(blocks):
+        sub.rows[q], sub.mul[q], sub.off[q] = lay.rows[b], lay.mul[b], lay.off[b]
+    sub.stride = lay.stride
+    return sub
+
+
 _lib = None
 
 
